@@ -1,0 +1,167 @@
+// Device-side BVH layout and traversal.
+//
+// The host hands over the reference's arrays verbatim (Node 48 B, RTTriangle 160 B, index list);
+// flx_trace.cu re-packs them once per scene into three 16-byte-vectorised streams:
+//
+//   inner node  64 B = 4 x float4   {L.min.xyz L.max.x} {L.max.yz R.min.xy} {R.min.z R.max.xyz}
+//                                    {leftRef, rightRef, -, -}
+//       both children's boxes live in the parent, so one node visit is one 64-byte fetch instead
+//       of the reference's 48 B node + two 48 B child fetches (src/bvh.cl:250, :284-285).
+//       ref >= 0: index of an inner node in this array;  ref < 0: ~ref = first leaf slot.
+//   leaf slot   48 B = 3 x float4   {v0.xyz, triIndex} {v1.xyz, lastFlag} {v2.xyz, matId}
+//       triangle positions stored in index-list order (one slot per entry of the reference's
+//       `indices`), so the indices[i] -> tris[...] double indirection of src/bvh.cl:262 is gone;
+//       lastFlag != 0 marks the last slot of a leaf, which replaces nPrims.
+//   shading rec 64 B = 4 x float4   n0.xyz n1.xyz n2.xyz uv0 uv1 uv2 matId, indexed by triangle id,
+//       read once per ray for the final hit only.
+//
+// Arithmetic and visit order are those of the reference (src/intersect.cl:41-93, src/bvh.cl:234-373):
+// near child first, left first on equal entry distance, children tested against the hit distance
+// current at the parent (no re-test on pop), leaf triangles in index order, strictly-closer wins.
+#pragma once
+#include "flx_math.cuh"
+
+struct DevBVH
+{
+    const float4 *nodes;  // 4 per inner node
+    const float4 *slots;  // 3 per leaf slot
+    const float4 *shade;  // 4 per triangle
+    int rootRef;
+};
+
+#define FLX_STACK_SIZE 64 // reference: uint stack[64] (src/bvh.cl:240)
+
+// src/intersect.cl:41-60 with dinv hoisted (same value each time => same bits)
+FLX_DEV bool slabTest(float bx0, float by0, float bz0, float bx1, float by1, float bz1,
+                      f3 o, f3 dinv, float tMaxPrev, float &tnear)
+{
+    const float lx = (bx0 - o.x) * dinv.x, ly = (by0 - o.y) * dinv.y, lz = (bz0 - o.z) * dinv.z;
+    const float hx = (bx1 - o.x) * dinv.x, hy = (by1 - o.y) * dinv.y, hz = (bz1 - o.z) * dinv.z;
+    const float tmin = fmaxf(fmaxf(fminf(lx, hx), fminf(ly, hy)), fminf(lz, hz));
+    const float tmax = fminf(fminf(fmaxf(lx, hx), fmaxf(ly, hy)), fmaxf(lz, hz));
+    tnear = tmin;
+    if (tmax < 0.0f) return false;
+    if (tmin > tmax) return false;
+    return tmin < tMaxPrev;
+}
+
+// src/intersect.cl:63-93 (Moeller-Trumbore, EPSILON 1e-12f)
+FLX_DEV bool triTest(f3 o, f3 d, f3 p0, f3 p1, f3 p2, float &t, float &u, float &v)
+{
+    const f3 s1 = p1 - p0;
+    const f3 s2 = p2 - p0;
+    const f3 pvec = cross(d, s2);
+    const float det = dot(s1, pvec);
+    if (fabsf(det) < 1e-12f) return false;
+    const float iDet = recip(det);
+    const f3 tvec = o - p0;
+    u = dot(tvec, pvec) * iDet;
+    if (u < 0.0f || u > 1.0f) return false;
+    const f3 qvec = cross(tvec, s1);
+    v = dot(d, qvec) * iDet;
+    if (v < 0.0f || u + v > 1.0f) return false;
+    t = dot(s2, qvec) * iDet;
+    if (t < 0.0f) return false;
+    return true;
+}
+
+struct RayHit
+{
+    float t, u, v;
+    int slot; // winning leaf slot, -1 = miss
+};
+
+// Closest hit (ANY=false): src/bvh.cl:234-310.  Any hit (ANY=true): src/bvh.cl:312-373, returns
+// with slot >= 0 as soon as a triangle with 0 < t < tmax is found.
+template <bool ANY>
+FLX_DEV RayHit traverse(const DevBVH &bvh, f3 o, f3 d, float tmax)
+{
+    RayHit best; best.t = tmax; best.u = 0.0f; best.v = 0.0f; best.slot = -1;
+    const f3 dinv = mk3(recip(d.x), recip(d.y), recip(d.z));
+    int stack[FLX_STACK_SIZE];
+    int sp = 0;
+    int cur = bvh.rootRef;
+    while (true)
+    {
+        if (cur >= 0)
+        {
+            const float4 *n = bvh.nodes + 4 * (size_t)cur;
+            const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
+            float lnear, rnear;
+            const bool lh = slabTest(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, dinv, best.t, lnear);
+            const bool rh = slabTest(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, dinv, best.t, rnear);
+            const int l = __float_as_int(n3.x), r = __float_as_int(n3.y);
+            if (lh && rh)
+            {
+                int nearRef = l, farRef = r;
+                if (rnear < lnear) { nearRef = r; farRef = l; }
+                stack[sp++] = farRef;
+                cur = nearRef;
+                continue;
+            }
+            if (lh) { cur = l; continue; }
+            if (rh) { cur = r; continue; }
+        }
+        else
+        {
+            int slot = ~cur;
+            while (true)
+            {
+                const float4 *q = bvh.slots + 3 * (size_t)slot;
+                const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2);
+                float t, u, v;
+                if (triTest(o, d, mk3(q0), mk3(q1), mk3(q2), t, u, v) && t > 0.0f && t < best.t)
+                {
+                    best.t = t; best.u = u; best.v = v; best.slot = slot;
+                    if (ANY) return best;
+                }
+                if (__float_as_int(q1.w) != 0) break;
+                slot++;
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    return best;
+}
+
+FLX_DEV f3 lerp3(float u, float v, f3 a, f3 b, f3 c) // src/utils.cl:25-28
+{
+    return (1.0f - u - v) * a + u * b + v * c;
+}
+
+// Final-hit attributes (src/bvh.cl:272-280): shading normal and uv from the 64-byte record.
+FLX_DEV void fetchHitAttribs(const DevBVH &bvh, const RayHit &h, f3 o, f3 d, int &triIndex, int &matId, f3 &P, f3 &N, float &uvx, float &uvy)
+{
+    const float4 *q = bvh.slots + 3 * (size_t)h.slot;
+    triIndex = __float_as_int(__ldg(q).w);
+    const float4 *s = bvh.shade + 4 * (size_t)triIndex;
+    const float4 s0 = __ldg(s), s1 = __ldg(s + 1), s2 = __ldg(s + 2), s3 = __ldg(s + 3);
+    matId = __float_as_int(s3.w);
+    P = o + h.t * d;
+    N = normalize(lerp3(h.u, h.v, mk3(s0.x, s0.y, s0.z), mk3(s0.w, s1.x, s1.y), mk3(s1.z, s1.w, s2.x)));
+    // only .xy of the interpolated texture coordinate is kept
+    const float w0 = 1.0f - h.u - h.v;
+    uvx = w0 * s2.y + h.u * s2.w + h.v * s3.y;
+    uvy = w0 * s2.z + h.u * s3.x + h.v * s3.z;
+}
+
+// src/intersect.cl:96-155 (area-light quad as two local triangles); used by ext and shadow stages
+struct AreaLightGeom { f3 tl, tr, bl, br, N; };
+
+FLX_DEV bool triLocal(f3 o, f3 d, f3 p0, f3 p1, f3 p2, float &tres)
+{
+    float t, u, v;
+    if (!triTest(o, d, p0, p1, p2, t, u, v)) return false;
+    if (t > tres) return false;
+    tres = t;
+    return true;
+}
+
+FLX_DEV bool intersectLight(const AreaLightGeom &g, f3 o, f3 d, float &t)
+{
+    if (dot(d, g.N) > 0.0f) return false;
+    const bool first = triLocal(o, d, g.tl, g.bl, g.br, t);
+    const bool second = triLocal(o, d, g.tl, g.br, g.tr, t);
+    return first || second;
+}

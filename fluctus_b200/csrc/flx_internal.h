@@ -1,0 +1,152 @@
+// Internal definitions shared by the .cu translation units of libfluctus_cuda.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/fluctus_cuda.h"
+#include "flx_bvh.cuh"
+
+// ---- path state in HBM ------------------------------------------------------------------------
+// The reference keeps GPUTaskState as 64 word-slots of SoA (256 B/path, src/geom.h:222-259) of
+// which 12 are float3 padding.  Here the 52 live words are grouped by the stage that writes them
+// into twelve float4 streams + four scalar streams (208 B/path), so every stage moves its fields
+// with 16-byte coalesced accesses and no stage has to read a field just to write it back:
+//
+//   ray0  orig.xyz       | lastPdfW          written by raygen, material      read by ext, logic
+//   ray1  dir.xyz        | pathLen (u32)     written by raygen, material; ext bumps .w
+//   hit0  P.xyz          | t                 written by ext (raygen/reset: empty hit)
+//   hit1  N.xyz          | hit.i (i32)       written by ext; logic rewrites N (shading normal/flip)
+//   hit2  uv.xy | matId (i32) | areaLightHit (i32)                     written by ext
+//   thr   T.xyz          | seed (u32)        written by raygen, logic (RR, rng), material
+//   acc   Ei.xyz         | pixelIndex (u32)  written by raygen, logic
+//   shw0  shadowOrig.xyz | shadowRayLen      written by logic (NEE)            read by shadow
+//   shw1  shadowDir.xyz  | lastCosTh         written by logic                  read by shadow, material
+//   nee0  lastEmission   | lastPdfDirect     written by logic
+//   nee1  lastBsdf       | lastPdfImplicit   written by material
+//   nee2  lastT.xyz      | (spare)           written by material
+//   scalars: lastSpecular (material), shadowBlocked (shadow, logic), logicFlags = backface |
+//            firstDiffuse<<1 (logic), lastPickProb (logic)
+struct PathState
+{
+    float4 *ray0, *ray1, *hit0, *hit1, *hit2, *thr, *acc, *shw0, *shw1, *nee0, *nee1, *nee2;
+    uint32_t *lastSpecular, *shadowBlocked, *logicFlags;
+    float *lastPickProb;
+};
+#define FLX_STATE_VEC_STREAMS 12
+#define FLX_STATE_SCALAR_STREAMS 4
+
+struct Queues
+{
+    uint32_t *q[FLX_NUM_QUEUES]; // N entries each (reference src/clcontext.cpp:130-138)
+    flx_queue_counters *counters; // device copy of QueueCounters
+};
+
+struct EnvMapDev
+{
+    const float4 *rgba; // w*h texels, alpha = 1 (what createEnvMap uploads)
+    const float *prob; const int *alias; const float *pdf;
+    int w, h;
+};
+
+struct MaterialsDev
+{
+    const flx_material *materials; int nMaterials;
+    const flx_tex_desc *textures; int nTextures;
+    const uint8_t *texels;
+    const flx_triangle *tris160; // original triangles: only read for normal-mapped hits (utils.cl:184-190)
+};
+
+struct FrameBuffers
+{
+    float4 *pixels, *preview, *denoiserAlbedo, *denoiserNormal, *denoiserAlbedoOut, *denoiserNormalOut;
+    uint32_t *spp;
+    uint32_t numPixels;
+};
+
+// Device-side bookkeeping that the reference does on the host between iterations
+// (tracer.cpp:761-773 statistics, clcontext.cpp:917-921 pixel cursor).
+struct RenderTotals
+{
+    unsigned long long primary, extension, shadow, samples, splatted, iterations;
+};
+
+struct StageTimer
+{
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+    double ms = 0.0; uint64_t launches = 0;
+};
+
+struct flx_ctx
+{
+    int device = 0;
+    cudaStream_t stream = nullptr; bool ownStream = false;
+    uint32_t N = 0;
+    int numSMs = 148;
+    std::string err;
+    uint64_t launches = 0;
+
+    // scene
+    DevBVH bvh{}; float4 *dNodes = nullptr, *dSlots = nullptr, *dShade = nullptr;
+    size_t nInner = 0, nSlots = 0, nTris = 0;
+    MaterialsDev mats{}; flx_material *dMaterials = nullptr; flx_tex_desc *dTextures = nullptr; uint8_t *dTexels = nullptr;
+    flx_triangle *dTris160 = nullptr;
+    bool sceneReady = false;
+    EnvMapDev env{}; float4 *dEnv = nullptr; float *dProb = nullptr, *dPdf = nullptr; int *dAlias = nullptr;
+
+    // wavefront
+    void *stateBlock = nullptr; PathState st{};
+    void *queueBlock = nullptr; Queues qs{};
+    uint32_t *dPixelIdx = nullptr;
+    RenderTotals *dTotals = nullptr;
+    FrameBuffers fb{}; void *fbBlock = nullptr;
+    flx_render_params params{}; bool paramsSet = false;
+    int denoiserAOV = 0; uint32_t seedOffset = 0;
+    flx_queue_counters *hCounters = nullptr; // pinned staging for async counter reads
+    std::vector<flx_queue_counters *> pendingCounterReads;
+
+    // graph for flx_render
+    cudaGraphExec_t graphExec = nullptr; bool graphValid = false;
+
+    // timing
+    bool timing = false; StageTimer timers[6];
+
+    // scratch for the host-buffer ray-cast entry points
+    void *dScratch = nullptr; size_t scratchBytes = 0;
+};
+
+// error helpers -----------------------------------------------------------------------------------
+int flx_fail(flx_ctx *ctx, int code, const std::string &msg);
+#define FLX_CUDA(ctx, call)                                                                         \
+    do {                                                                                            \
+        cudaError_t e__ = (call);                                                                   \
+        if (e__ != cudaSuccess)                                                                     \
+            return flx_fail(ctx, FLX_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+    } while (0)
+
+// launch geometry: persistent grid-stride kernels sized to the machine (148 SMs on B200)
+static inline int flx_grid(const flx_ctx *ctx, int blocksPerSM) { return ctx->numSMs * blocksPerSM; }
+
+// implemented in flx_trace.cu
+int flx_repack_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, const uint32_t *indices, size_t n_indices,
+                     const flx_node *nodes, size_t n_nodes);
+int flx_launch_ext(flx_ctx *ctx);
+int flx_launch_shadow(flx_ctx *ctx);
+int flx_launch_trace_batch(flx_ctx *ctx, const float4 *dRays, size_t n, int32_t *dHitI, float *dHitT, flx_hit *dHits);
+int flx_launch_any_batch(flx_ctx *ctx, const float4 *dRays, size_t n, uint8_t *dOcc);
+
+// implemented in flx_wavefront.cu
+int flx_launch_reset(flx_ctx *ctx);
+int flx_launch_raygen(flx_ctx *ctx);
+int flx_launch_logic(flx_ctx *ctx, int firstIteration);
+int flx_launch_materials(flx_ctx *ctx);
+int flx_launch_postprocess(flx_ctx *ctx);
+int flx_launch_bookkeeping(flx_ctx *ctx); // counters -> totals, pixel cursor advance, clear
+int flx_launch_advance_pixel(flx_ctx *ctx, uint32_t numPixels, uint32_t numNew);
+int flx_launch_export_state(flx_ctx *ctx, uint32_t *dSlots64xN);
+int flx_launch_import_state(flx_ctx *ctx, const uint32_t *dSlots64xN);
+
+// implemented in flx_context.cu
+int flx_ready(flx_ctx *ctx, bool needScene);
+void flx_invalidate_graph(flx_ctx *ctx);
+void flx_drain_timers(flx_ctx *ctx);

@@ -1,0 +1,363 @@
+// The logic stage (path state machine, splat, next-event-estimation sample generation, queue
+// compaction) and the material-queue shaders.
+// Behavioural contract: reference src/wf_logic.cl:14-344 and src/wf_mat_*.cl (identical bodies).
+#include "flx_bxdf.cuh"
+
+#define FLX_WF_THREADS 256
+
+FLX_DEV uint32_t warpPush(uint32_t *counter, bool pred) // see flx_wavefront.cu
+{
+    const unsigned mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0u) return 0u;
+    const unsigned lane = threadIdx.x & 31u;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if ((int)lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+}
+
+// utils.cl:174-207 — only reached for materials with a normal map
+FLX_DEV f3 tangentSpaceNormal(f3 hitN, float uvx, float uvy, int hitI, int mapN, const MaterialsDev &md)
+{
+    f3 texNormal = readTexture(uvx, uvy, md.textures[mapN], md.texels);
+    texNormal = texNormal + texNormal - mk3(1.0f, 1.0f, 1.0f);
+    const flx_triangle *t = md.tris160 + hitI;
+    const f3 e1 = ld3(t->v1.p) - ld3(t->v0.p);
+    const f3 e2 = ld3(t->v2.p) - ld3(t->v0.p);
+    const f3 t1 = ld3(t->v1.t) - ld3(t->v0.t);
+    const f3 t2 = ld3(t->v2.t) - ld3(t->v0.t);
+    const float det = (t1.x * t2.y - t1.y * t2.x);
+    if (det == 0.0f) return hitN;
+    const float invDet = recip(det);
+    const f3 T = normalize(invDet * (e1 * t2.y - e2 * t1.y));
+    const f3 B = normalize(invDet * (e2 * t1.x - e1 * t2.x));
+    f3 N;
+    N.x = T.x * texNormal.x + B.x * texNormal.y + hitN.x * texNormal.z;
+    N.y = T.y * texNormal.x + B.y * texNormal.y + hitN.y * texNormal.z;
+    N.z = T.z * texNormal.x + B.z * texNormal.y + hitN.z * texNormal.z;
+    return normalize(N);
+}
+
+// material type -> queue (wf_logic.cl:352-407); MIXED goes with diffuse
+FLX_DEV int materialQueueOf(int type, bool separate)
+{
+    if (!separate) return FLX_Q_DIFFUSE; // -DWF_SINGLE_MAT_QUEUE
+    switch (type)
+    {
+    case FLX_BXDF_DIFFUSE: case FLX_BXDF_MIXED: return FLX_Q_DIFFUSE;
+    case FLX_BXDF_GLOSSY: return FLX_Q_GLOSSY;
+    case FLX_BXDF_GGX_ROUGH_REFLECTION: return FLX_Q_GGX_REFL;
+    case FLX_BXDF_GGX_ROUGH_DIELECTRIC: return FLX_Q_GGX_REFR;
+    case FLX_BXDF_IDEAL_REFLECTION: case FLX_BXDF_IDEAL_DIELECTRIC: return FLX_Q_DELTA;
+    case FLX_BXDF_EMISSIVE: return FLX_Q_EMISSIVE;
+    }
+    return -1;
+}
+
+FLX_DEV uint32_t *counterOf(flx_queue_counters *c, int q) { return ((uint32_t *)c) + q; } // same order as FLX_Q_*
+
+__global__ void __launch_bounds__(FLX_WF_THREADS)
+k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env, uint32_t N, uint32_t firstIteration,
+        int denoiserAOV, const __grid_constant__ flx_render_params params)
+{
+    const uint32_t numPixels = params.width * params.height;
+    const uint32_t maxId = firstIteration ? min(numPixels, N) : N;
+    const uint32_t rounded = (maxId + 31u) & ~31u;
+    const bool checkSpp = params.maxSpp > 0u; // -DCHECK_SPP
+    const bool separate = params.wfSeparateQueues != 0u;
+
+    for (uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x; gid < rounded; gid += gridDim.x * blockDim.x)
+    {
+        const bool valid = gid < maxId;
+        bool terminate = false, pushShadow = false, splatted = false;
+        int matQ = -1;
+
+        if (valid)
+        {
+            const float4 thr = st.thr[gid], r0 = st.ray0[gid], r1 = st.ray1[gid];
+            const float4 h0 = st.hit0[gid], h1 = st.hit1[gid], h2 = st.hit2[gid], acc = st.acc[gid];
+            f3 T = mk3(thr);
+            uint32_t seed = __float_as_uint(thr.w);
+            const uint32_t len = __float_as_uint(r1.w);
+            const f3 rayOrig = mk3(r0), rayDir = mk3(r1);
+            const float lastPdfW = r0.w;
+            const f3 hitP = mk3(h0);
+            f3 hitN = mk3(h1);
+            const int hitI = __float_as_int(h1.w), matId = __float_as_int(h2.z), areaLightHit = __float_as_int(h2.w);
+            f3 Ei = mk3(acc);
+            const uint32_t pixIdx = __float_as_uint(acc.w);
+
+            // Russian roulette (:59-74)
+            terminate = params.maxBounces > 0u && (len >= params.maxBounces + 1u);
+            if (!terminate && params.useRoulette && len > 5u)
+            {
+                const float contProb = clampf(luminance(T), 0.01f, 0.5f);
+                terminate = (rnd(seed) > contProb);
+                T /= contProb;
+            }
+            bool maxSamplesReached = false;
+            if (checkSpp && fb.spp[pixIdx] >= params.maxSpp) { terminate = true; maxSamplesReached = true; } // :76-84
+            if (isZero(T) || lastPdfW == 0.0f) terminate = true;                                             // :87-88
+
+            if (hitI < 0 && !terminate) // escaped: implicit environment sample with MIS (:99-122)
+            {
+                float weight = 1.0f;
+                f3 bg = mk3(0.0f);
+                if (params.useEnvMap)
+                {
+                    if (len == 1u || params.sampleImpl) bg = evalEnvMapDir(env, rayDir) * params.envMapStrength;
+                    if (params.sampleImpl && params.sampleExpl && len > 1u && !st.lastSpecular[gid])
+                    {
+                        const float lightPickProb = st.lastPickProb[gid];
+                        const float directPdfW = envMapPdf(env, rayDir);
+                        weight = (lastPdfW * lightPickProb) / (lastPdfW * lightPickProb + directPdfW);
+                    }
+                }
+                Ei = Ei + weight * T * bg;
+                terminate = true;
+            }
+            else if (params.useAreaLight && areaLightHit && !terminate) // implicit area-light hit (:126-146)
+            {
+                float misWeight = 1.0f;
+                if (params.sampleExpl && len > 1u && !st.lastSpecular[gid])
+                {
+                    const float directPdfA = recip(4.0f * params.areaLight.size.x * params.areaLight.size.y);
+                    const float directPdfW = pdfAtoW(directPdfA, length(hitP - rayOrig), -dot(rayDir, hitN));
+                    const float lightPickProb = st.lastPickProb[gid];
+                    misWeight = lastPdfW / (lastPdfW + directPdfW * lightPickProb);
+                }
+                Ei = Ei + T * misWeight * ld3(params.areaLight.E);
+                terminate = true;
+            }
+
+            // resolve the NEE sample whose shadow ray came back unoccluded (:150-168)
+            if (st.shadowBlocked[gid] == 0u)
+            {
+                const float4 n0 = st.nee0[gid], n1 = st.nee1[gid], n2 = st.nee2[gid];
+                const float cosTh = st.shw1[gid].w;
+                const float lightPickProb = st.lastPickProb[gid];
+                const f3 contrib = mk3(n1) * mk3(n2) * mk3(n0) * cosTh / (lightPickProb * n0.w + (float)(params.sampleImpl) * n1.w);
+                Ei = Ei + contrib;
+            }
+
+            if (terminate) // splat and hand the slot back to raygen (:171-205)
+            {
+                bool admit;
+                if (checkSpp)
+                {
+                    admit = false;
+                    if (!maxSamplesReached) admit = (atomicAdd(&fb.spp[pixIdx], 1u) <= params.maxSpp) && len > 0u; // `<=`: quirk kept
+                    if (fb.spp[pixIdx] > params.maxSpp) fb.spp[pixIdx] = params.maxSpp;
+                    splatted = admit;
+                }
+                else admit = len > 0u;
+                if (admit) atomicAdd(&fb.pixels[pixIdx], make_float4(Ei.x, Ei.y, Ei.z, 1.0f));
+            }
+            else
+            {
+                // surviving path: shading normal, backface flip (:208-241)
+                const flx_material *mp = md.materials + matId;
+                const float4 mtail = __ldg(((const float4 *)mp) + 5); // map_Ks, map_N, type, pad
+                const int mapN = __float_as_int(mtail.y), mtype = __float_as_int(mtail.z);
+                if (mapN != -1) hitN = tangentSpaceNormal(hitN, h2.x, h2.y, hitI, mapN, md);
+                const bool backface = dot(hitN, rayDir) > 0.0f;
+                if (backface) hitN = -hitN;
+                const f3 orig = hitP - 1e-3f * rayDir;
+                uint32_t flags = backface ? 1u : 0u;
+
+                if (denoiserAOV) // -DUSE_OPTIX_DENOISER accumulation (:214-237)
+                {
+                    if (len == 1u)
+                    {
+                        const f3 c1 = ld3(params.camera.right), c2 = ld3(params.camera.up), c3 = -ld3(params.camera.dir);
+                        atomicAdd(&fb.denoiserNormal[pixIdx], make_float4(dot(c1, hitN), dot(c2, hitN), dot(c3, hitN), 1.0f));
+                    }
+                    const uint32_t firstDiffuse = (st.logicFlags[gid] >> 1) & 1u;
+                    flags |= firstDiffuse << 1;
+                    if (!FLX_BXDF_IS_SINGULAR(mtype) && !firstDiffuse)
+                    {
+                        flags |= 2u;
+                        const float4 kd = __ldg((const float4 *)mp), m4 = __ldg(((const float4 *)mp) + 4);
+                        const f3 albedo = matGetFloat3(mk3(kd), h2.x, h2.y, __float_as_int(m4.w), md);
+                        atomicAdd(&fb.denoiserAlbedo[pixIdx], make_float4(albedo.x, albedo.y, albedo.z, 1.0f));
+                    }
+                }
+                st.hit1[gid] = mk4i(hitN, hitI);
+                st.logicFlags[gid] = flags;
+
+                if (params.sampleExpl) // -DSAMPLE_EXPLICIT (:243-333)
+                {
+                    st.shadowBlocked[gid] = 1u;
+                    if (!FLX_BXDF_IS_SINGULAR(mtype))
+                    {
+                        const uint32_t nLights = params.useEnvMap + params.useAreaLight;
+                        const float envMapProb = (float)params.useEnvMap / (float)max(1u, nLights);
+                        const bool useEnv = rnd(seed) < envMapProb;
+                        const bool useArea = !useEnv && params.useAreaLight;
+                        if (useEnv && params.useEnvMap)
+                        {
+                            f3 L; float directPdfW;
+                            sampleEnvMapAlias(rnd(seed), L, directPdfW, env);
+                            const float lenL = params.worldRadius + params.worldRadius;
+                            const float cosTh = fmaxf(0.0f, dot(L, hitN));
+                            const f3 envMapLi = evalEnvMapDir(env, L) * params.envMapStrength;
+                            st.shw0[gid] = mk4(orig, lenL);
+                            st.shw1[gid] = mk4(L, cosTh);
+                            st.nee0[gid] = mk4(envMapLi, directPdfW);
+                            st.lastPickProb[gid] = envMapProb;
+                            pushShadow = true;
+                        }
+                        if (useArea)
+                        {
+                            float directPdfA; f3 posL;
+                            sampleAreaLight(params.areaLight, directPdfA, posL, seed);
+                            f3 L = posL - orig;
+                            const float cosLight = fmaxf(dot(ld3(params.areaLight.N), -L), 0.0f);
+                            if (cosLight > 0.0f) // only samples that see the emitting side
+                            {
+                                const float lenL0 = length(L);
+                                const float lenL = lenL0 * 0.995f;
+                                const float invLEN = recip(lenL0);
+                                L *= invLEN;
+                                const float directPdfW = pdfAtoW(directPdfA, lenL, cosLight * invLEN);
+                                const float cosTh = fmaxf(0.0f, dot(L, hitN));
+                                st.shw0[gid] = mk4(orig, lenL);
+                                st.shw1[gid] = mk4(L, cosTh);
+                                st.nee0[gid] = mk4(ld3(params.areaLight.E), directPdfW);
+                                st.lastPickProb[gid] = 1.0f - envMapProb;
+                                pushShadow = true;
+                            }
+                        }
+                    }
+                }
+                matQ = materialQueueOf(mtype, separate);
+            }
+            st.thr[gid] = mk4u(T, seed);
+            st.acc[gid] = mk4u(Ei, pixIdx);
+        }
+
+        // ---- warp-aggregated compaction into the raygen / shadow / material queues ----------------
+        {
+            const uint32_t slot = warpPush(&qs.counters->raygenQueue, valid && terminate);
+            if (valid && terminate) qs.q[FLX_Q_RAYGEN][slot] = gid;
+        }
+        {
+            const uint32_t slot = warpPush(&qs.counters->shadowQueue, pushShadow);
+            if (pushShadow) qs.q[FLX_Q_SHADOW][slot] = gid;
+        }
+        if (!separate)
+        {
+            const uint32_t slot = warpPush(&qs.counters->diffuseQueue, matQ >= 0);
+            if (matQ >= 0) qs.q[FLX_Q_DIFFUSE][slot] = gid;
+        }
+        else
+        {
+#pragma unroll
+            for (int q = FLX_Q_DIFFUSE; q <= FLX_Q_EMISSIVE; q++)
+            {
+                const uint32_t slot = warpPush(counterOf(qs.counters, q), matQ == q);
+                if (matQ == q) qs.q[q][slot] = gid;
+            }
+        }
+        if (checkSpp)
+        {
+            const unsigned m = __ballot_sync(0xffffffffu, splatted);
+            if ((threadIdx.x & 31u) == 0u && m) atomicAdd(&qs.counters->splattedSamples, (uint32_t)__popc(m));
+        }
+    }
+}
+
+// Shared body of the material stages (wf_mat_diffuse.cl:7-66 and its five siblings, wf_mat_all.cl).
+// TYPES is the compile-time set of BxDFs this instantiation can meet in its queue.
+template <int TYPES>
+__global__ void __launch_bounds__(FLX_WF_THREADS)
+k_material(PathState st, Queues qs, MaterialsDev md, int queueId)
+{
+    const uint32_t qlen = *counterOf(qs.counters, queueId);
+    const uint32_t rounded = (qlen + 31u) & ~31u;
+    const uint32_t *__restrict__ queue = qs.q[queueId];
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < rounded; k += gridDim.x * blockDim.x)
+    {
+        const bool valid = k < qlen;
+        uint32_t gid = 0;
+        if (valid)
+        {
+            gid = queue[k];
+            const float4 thr = st.thr[gid], r1 = st.ray1[gid], h0 = st.hit0[gid], h1 = st.hit1[gid], h2 = st.hit2[gid];
+            uint32_t seed = __float_as_uint(thr.w);
+            SurfHit hit; hit.N = mk3(h1); hit.uvx = h2.x; hit.uvy = h2.y;
+            const Mat mat = loadMat(md.materials + __float_as_int(h2.z));
+            const bool backface = (st.logicFlags[gid] & 1u) != 0u;
+            const f3 dirIn = mk3(r1);
+            const f3 L = mk3(st.shw1[gid]);
+
+            const f3 bsdfNEE = bxdfEval<TYPES>(hit, mat, backface, md, dirIn, L);
+            const float bsdfPdfW = fmaxf(0.0f, bxdfPdf<TYPES>(hit, mat, backface, md, dirIn, L));
+            st.nee1[gid] = mk4(bsdfNEE, bsdfPdfW);
+
+            float pdfW = 0.0f;     // the reference leaves these unset for emissive / rejected glossy
+            f3 newDir = mk3(0.0f); // samples; the oracle pins them to 0 and so do we
+            const f3 bsdf = bxdfSample<TYPES>(hit, mat, backface, md, dirIn, newDir, pdfW, seed);
+
+            const f3 oldT = mk3(thr);
+            f3 newT;
+            if (pdfW == 0.0f || isZero(bsdf)) newT = mk3(0.0f);
+            else newT = oldT * bsdf * dot(hit.N, newDir) / pdfW;
+            const f3 orig = mk3(h0) + 1e-4f * newDir;
+
+            st.nee2[gid] = mk4(oldT, 0.0f);
+            st.thr[gid] = mk4u(newT, seed);
+            st.ray0[gid] = mk4(orig, pdfW);
+            st.ray1[gid] = make_float4(newDir.x, newDir.y, newDir.z, r1.w);
+            st.lastSpecular[gid] = FLX_BXDF_IS_SINGULAR(mat.type) ? 1u : 0u;
+        }
+        const uint32_t slot = warpPush(&qs.counters->extensionQueue, valid);
+        if (valid) qs.q[FLX_Q_EXTENSION][slot] = gid;
+    }
+}
+
+// ---- launchers -----------------------------------------------------------------------------------
+static inline int wfGrid(const flx_ctx *ctx, uint64_t items)
+{
+    const uint64_t blocks = (items + FLX_WF_THREADS - 1) / FLX_WF_THREADS;
+    const uint64_t cap = (uint64_t)ctx->numSMs * 8;
+    return (int)(blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
+}
+#define FLX_LAUNCHED(ctx) do { (ctx)->launches++; FLX_CUDA(ctx, cudaGetLastError()); } while (0)
+
+int flx_launch_logic(flx_ctx *ctx, int firstIteration)
+{
+    k_logic<<<wfGrid(ctx, ctx->N), FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->fb, ctx->mats, ctx->env, ctx->N,
+                                                                     (uint32_t)(firstIteration != 0), ctx->denoiserAOV, ctx->params);
+    FLX_LAUNCHED(ctx);
+    return FLX_OK;
+}
+
+#define FLX_ALL_TYPES (FLX_BXDF_DIFFUSE | FLX_BXDF_GLOSSY | FLX_BXDF_GGX_ROUGH_REFLECTION | FLX_BXDF_IDEAL_REFLECTION | \
+                       FLX_BXDF_GGX_ROUGH_DIELECTRIC | FLX_BXDF_IDEAL_DIELECTRIC | FLX_BXDF_EMISSIVE)
+
+// CLContext::enqueueWfMaterialKernels (clcontext.cpp:816-831)
+int flx_launch_materials(flx_ctx *ctx)
+{
+    const int grid = wfGrid(ctx, ctx->N);
+    if (!ctx->params.wfSeparateQueues)
+    {
+        k_material<FLX_ALL_TYPES><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_DIFFUSE);
+        FLX_LAUNCHED(ctx);
+        return FLX_OK;
+    }
+    k_material<FLX_BXDF_DIFFUSE><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_DIFFUSE);
+    FLX_LAUNCHED(ctx);
+    k_material<FLX_BXDF_GLOSSY><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_GLOSSY);
+    FLX_LAUNCHED(ctx);
+    k_material<FLX_BXDF_GGX_ROUGH_REFLECTION><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_GGX_REFL);
+    FLX_LAUNCHED(ctx);
+    k_material<FLX_BXDF_GGX_ROUGH_DIELECTRIC><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_GGX_REFR);
+    FLX_LAUNCHED(ctx);
+    k_material<FLX_BXDF_IDEAL_REFLECTION | FLX_BXDF_IDEAL_DIELECTRIC><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_DELTA);
+    FLX_LAUNCHED(ctx);
+    k_material<FLX_BXDF_EMISSIVE><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_EMISSIVE);
+    FLX_LAUNCHED(ctx);
+    return FLX_OK;
+}

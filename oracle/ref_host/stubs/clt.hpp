@@ -1,0 +1,3 @@
+#pragma once
+#include "cl2.hpp"
+namespace clt { class Kernel; }

@@ -1,0 +1,3 @@
+#pragma once
+#include <functional>
+namespace nanogui { class Screen; class Window; class Label; class ProgressBar; }
