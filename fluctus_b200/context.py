@@ -1,0 +1,222 @@
+"""CudaContext — host-side mirror of the reference's `class CLContext` (src/clcontext.hpp:26-215)
+on top of the C-ABI.  Method names, argument meaning and error behaviour follow the reference so
+that the render loop in tracer.py reads like Tracer::update / runBenchmarkFromFile."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .abi import COUNTERS_DT, HIT_DT, PARAMS_DT, QUEUES, TEX_DT
+from ._lib import FluctusError, V
+
+BUF_PIXELS, BUF_PREVIEW, BUF_DENOISER_ALBEDO, BUF_DENOISER_NORMAL, BUF_SPP, BUF_ALBEDO_OUT, BUF_NORMAL_OUT = range(7)
+STAGE_EXT, STAGE_SHADOW, STAGE_LOGIC, STAGE_RAYGEN, STAGE_MATERIALS, STAGE_TRACE_BATCH = range(6)
+
+
+def _p(a):
+    return a.ctypes.data_as(V) if a is not None else None
+
+
+class CudaContext:
+    def __init__(self, num_tasks=1 << 20, device=0, stream=None):
+        self.L = _lib.load()
+        h = V()
+        rc = self.L.flx_create(C.byref(h), int(device), int(num_tasks), V(stream) if stream else None)
+        if rc != 0:
+            raise FluctusError(self.L.flx_last_error(None).decode())
+        self.h = h
+        self.NUM_TASKS = int(num_tasks)
+        self.width = self.height = 0
+        self._pending = []  # keeps counter arrays alive until finishQueue
+
+    # ---- plumbing
+    def _check(self, rc):
+        if rc != 0:
+            raise FluctusError(self.L.flx_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.flx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def getNumTasks(self):
+        return int(self.L.flx_num_tasks(self.h))
+
+    @property
+    def stream(self):
+        return self.L.flx_stream(self.h)
+
+    # ---- uploads
+    def uploadSceneData(self, scene):
+        """scene: dict with tris (TRI_DT), indices (u32), nodes (NODE_DT), materials (MAT_DT) and optionally
+        textures (TEX_DT) + texels (u8) — what CLContext::uploadSceneData takes from BVH* and Scene*."""
+        tris = np.ascontiguousarray(scene["tris"])
+        idx = np.ascontiguousarray(scene["indices"], np.uint32)
+        nodes = np.ascontiguousarray(scene["nodes"])
+        mats = np.ascontiguousarray(scene["materials"])
+        tex = np.ascontiguousarray(scene.get("textures", np.zeros(0, TEX_DT)))
+        texels = np.ascontiguousarray(scene.get("texels", np.zeros(0, np.uint8)), np.uint8)
+        assert tris.dtype.itemsize == 160 and nodes.dtype.itemsize == 48 and mats.dtype.itemsize == 96
+        self._check(self.L.flx_upload_scene(self.h, _p(tris), len(tris), _p(idx), len(idx), _p(nodes), len(nodes),
+                                            _p(mats), len(mats), _p(tex) if len(tex) else None, len(tex),
+                                            _p(texels) if len(texels) else None, texels.nbytes))
+
+    def createEnvMap(self, env):
+        rgb = np.ascontiguousarray(env["rgb"], np.float32)
+        h, w = rgb.shape[:2]
+        prob = np.ascontiguousarray(env["prob"], np.float32)
+        alias = np.ascontiguousarray(env["alias"], np.int32)
+        pdf = np.ascontiguousarray(env["pdf"], np.float32)
+        self._check(self.L.flx_upload_envmap(self.h, _p(rgb), w, h, _p(prob), _p(alias), _p(pdf)))
+
+    def setupPixelStorage(self, width, height):
+        self._check(self.L.flx_resize(self.h, int(width), int(height)))
+        self.width, self.height = int(width), int(height)
+
+    def updateParams(self, params):
+        p = np.ascontiguousarray(params).view(np.uint8).reshape(-1)
+        assert p.size == PARAMS_DT.itemsize
+        self._check(self.L.flx_update_params(self.h, _p(p)))
+        pr = p.view(PARAMS_DT)[0]
+        self.width, self.height = int(pr["width"]), int(pr["height"])
+
+    def setOptions(self, denoiser_aov=False, seed_offset=0):
+        self._check(self.L.flx_set_options(self.h, int(denoiser_aov), int(seed_offset)))
+
+    def recompileKernels(self, setArgs=False):
+        """No-op: every specialisation is compiled ahead of time and picked by updateParams."""
+
+    # ---- pixel cursor
+    def resetPixelIndex(self): self._check(self.L.flx_reset_pixel_index(self.h))
+    def setPixelIndex(self, v): self._check(self.L.flx_set_pixel_index(self.h, int(v)))
+    def updatePixelIndex(self, numPixels, numNewPaths): self._check(self.L.flx_update_pixel_index(self.h, int(numPixels), int(numNewPaths)))
+
+    # ---- stages (the params argument is kept for signature parity; the device copy is the one set by updateParams)
+    def enqueueWfResetKernel(self, params=None): self._check(self.L.flx_wf_reset(self.h))
+    def enqueueWfRaygenKernel(self, params=None): self._check(self.L.flx_wf_raygen(self.h))
+    def enqueueWfLogicKernel(self, params=None, firstIteration=False): self._check(self.L.flx_wf_logic(self.h, int(bool(firstIteration))))
+    def enqueueWfMaterialKernels(self, params=None): self._check(self.L.flx_wf_materials(self.h))
+    def enqueueWfExtRayKernel(self, params=None): self._check(self.L.flx_wf_ext(self.h))
+    def enqueueWfShadowRayKernel(self, params=None): self._check(self.L.flx_wf_shadow(self.h))
+    def enqueueClearWfQueues(self): self._check(self.L.flx_wf_clear_queues(self.h))
+    def enqueuePostprocessKernel(self, params=None): self._check(self.L.flx_postprocess(self.h))
+
+    def enqueueGetCounters(self):
+        """Asynchronous like the reference: the returned record is valid after finishQueue()."""
+        cnt = np.zeros(1, COUNTERS_DT)
+        self._pending.append(cnt)
+        self._check(self.L.flx_get_counters(self.h, _p(cnt)))
+        return cnt[0]
+
+    def finishQueue(self):
+        self._check(self.L.flx_finish(self.h))
+        self._pending.clear()
+
+    # ---- headless render entry
+    def render(self, iterations, reset=False):
+        self._check(self.L.flx_render(self.h, int(iterations), int(bool(reset))))
+
+    def getRenderTotals(self):
+        t = np.zeros(6, np.uint64)
+        self._check(self.L.flx_get_render_totals(self.h, _p(t)))
+        return dict(zip(("primary", "extension", "shadow", "samples", "splatted", "iterations"), (int(x) for x in t)))
+
+    # ---- results
+    def readPixels(self, which=BUF_PIXELS, out=None):
+        n = self.width * self.height
+        if out is None:
+            out = np.empty(n, np.uint32) if which == BUF_SPP else np.empty((n, 4), np.float32)
+        self._check(self.L.flx_read_pixels(self.h, int(which), _p(out), out.nbytes))
+        return out
+
+    def writePixels(self, which, data):
+        data = np.ascontiguousarray(data)
+        self._check(self.L.flx_write_pixels(self.h, int(which), _p(data), data.nbytes))
+
+    def devicePtr(self, which=BUF_PIXELS):
+        return self.L.flx_device_ptr(self.h, int(which))
+
+    def pickSingle(self, NDCx, NDCy):
+        hit = np.zeros(1, HIT_DT)
+        self._check(self.L.flx_pick(self.h, float(NDCx), float(NDCy), _p(hit)))
+        return hit[0]
+
+    # ---- ray casting
+    def traceClosest(self, rays, want_hits=False):
+        rays = np.ascontiguousarray(rays, np.float32)
+        n = rays.shape[0]
+        hit_i, hit_t = np.empty(n, np.int32), np.empty(n, np.float32)
+        hits = np.zeros(n, HIT_DT) if want_hits else None
+        self._check(self.L.flx_trace_closest(self.h, _p(rays), n, _p(hit_i), _p(hit_t), _p(hits)))
+        return (hit_i, hit_t, hits) if want_hits else (hit_i, hit_t)
+
+    def traceAny(self, rays):
+        rays = np.ascontiguousarray(rays, np.float32)
+        occ = np.empty(rays.shape[0], np.uint8)
+        self._check(self.L.flx_trace_any(self.h, _p(rays), rays.shape[0], _p(occ)))
+        return occ
+
+    def traceClosestDevice(self, d_rays, n, d_hit_i=None, d_hit_t=None, d_hits=None):
+        self._check(self.L.flx_trace_closest_device(self.h, V(d_rays), int(n), V(d_hit_i) if d_hit_i else None,
+                                                    V(d_hit_t) if d_hit_t else None, V(d_hits) if d_hits else None))
+
+    def traceAnyDevice(self, d_rays, n, d_occ):
+        self._check(self.L.flx_trace_any_device(self.h, V(d_rays), int(n), V(d_occ)))
+
+    # ---- state inspection (stage parity)
+    def exportState(self):
+        s = np.empty((64, self.NUM_TASKS), np.uint32)
+        self._check(self.L.flx_export_state(self.h, _p(s)))
+        return s
+
+    def importState(self, state64):
+        s = np.ascontiguousarray(state64, np.uint32)
+        assert s.shape == (64, self.NUM_TASKS)
+        self._check(self.L.flx_import_state(self.h, _p(s)))
+
+    def readQueue(self, q, n):
+        q = QUEUES.index(q) if isinstance(q, str) else int(q)
+        out = np.empty(int(n), np.uint32)
+        self._check(self.L.flx_read_queue(self.h, q, _p(out), int(n)))
+        return out
+
+    def writeQueue(self, q, data):
+        q = QUEUES.index(q) if isinstance(q, str) else int(q)
+        data = np.ascontiguousarray(data, np.uint32)
+        self._check(self.L.flx_write_queue(self.h, q, _p(data), len(data)))
+
+    def setCounters(self, cnt):
+        c = np.ascontiguousarray(cnt).view(np.uint8).reshape(-1)
+        assert c.size == 40
+        self._check(self.L.flx_set_counters(self.h, _p(c)))
+
+    def getCounters(self):
+        """Synchronous convenience: enqueueGetCounters + finishQueue."""
+        c = self.enqueueGetCounters()
+        self.finishQueue()
+        return c.copy()
+
+    # ---- instrumentation
+    def launchCount(self): return int(self.L.flx_launch_count(self.h))
+    def enableTiming(self, on=True): self._check(self.L.flx_enable_timing(self.h, int(bool(on))))
+
+    def setTraceCounting(self, on=True): self._check(self.L.flx_set_trace_counting(self.h, int(bool(on))))
+
+    def traceCounters(self):
+        """dict group -> {inner, leaf, tri, hits, rays}; groups ext, shadow, batch_closest, batch_any."""
+        c = np.zeros(20, np.uint64)
+        self._check(self.L.flx_get_trace_counters(self.h, _p(c)))
+        names = ("inner", "leaf", "tri", "hits", "rays")
+        return {g: dict(zip(names, (int(x) for x in c[5 * k:5 * k + 5])))
+                for k, g in enumerate(("ext", "shadow", "batch_closest", "batch_any"))}
+
+    def kernelTime(self, stage):
+        ms, n = C.c_double(), C.c_uint64()
+        self._check(self.L.flx_get_kernel_time(self.h, int(stage), C.byref(ms), C.byref(n)))
+        return ms.value, n.value

@@ -330,6 +330,23 @@ int flx_enable_timing(flx_ctx *ctx, int enable)
     return FLX_OK;
 }
 
+int flx_set_trace_counting(flx_ctx *ctx, int enable)
+{
+    FLX_CHECK_CTX(ctx); FLX_CUDA(ctx, cudaSetDevice(ctx->device));
+    if ((enable != 0) != ctx->counting) flx_invalidate_graph(ctx);
+    ctx->counting = enable != 0;
+    if (enable) FLX_CUDA(ctx, cudaMemsetAsync(ctx->dTraceStats, 0, 20 * sizeof(unsigned long long), ctx->stream));
+    return FLX_OK;
+}
+
+int flx_get_trace_counters(flx_ctx *ctx, uint64_t out[20])
+{
+    FLX_CHECK_CTX(ctx); FLX_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!out) return flx_fail(ctx, FLX_ERR_ARG, "flx_get_trace_counters: null output");
+    FLX_CUDA(ctx, cudaMemcpyAsync(out, ctx->dTraceStats, 20 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    return flx_finish(ctx);
+}
+
 int flx_get_kernel_time(flx_ctx *ctx, int stage, double *ms, uint64_t *launches)
 {
     FLX_CHECK_CTX(ctx);

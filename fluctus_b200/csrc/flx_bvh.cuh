@@ -71,10 +71,14 @@ struct RayHit
     int slot; // winning leaf slot, -1 = miss
 };
 
+// Visit counters for the algorithmic-bytes figure: inner-node pops, leaf visits,
+// triangle tests.  Only the COUNT=true instantiations touch them; the timed kernels do not.
+struct TravCount { unsigned int inner, leaf, tri; };
+
 // Closest hit (ANY=false): src/bvh.cl:234-310.  Any hit (ANY=true): src/bvh.cl:312-373, returns
 // with slot >= 0 as soon as a triangle with 0 < t < tmax is found.
-template <bool ANY>
-FLX_DEV RayHit traverse(const DevBVH &bvh, f3 o, f3 d, float tmax)
+template <bool ANY, bool COUNT = false>
+FLX_DEV RayHit traverse(const DevBVH &bvh, f3 o, f3 d, float tmax, TravCount *cnt = nullptr)
 {
     RayHit best; best.t = tmax; best.u = 0.0f; best.v = 0.0f; best.slot = -1;
     const f3 dinv = mk3(recip(d.x), recip(d.y), recip(d.z));
@@ -85,6 +89,7 @@ FLX_DEV RayHit traverse(const DevBVH &bvh, f3 o, f3 d, float tmax)
     {
         if (cur >= 0)
         {
+            if (COUNT) cnt->inner++;
             const float4 *n = bvh.nodes + 4 * (size_t)cur;
             const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
             float lnear, rnear;
@@ -105,8 +110,10 @@ FLX_DEV RayHit traverse(const DevBVH &bvh, f3 o, f3 d, float tmax)
         else
         {
             int slot = ~cur;
+            if (COUNT) cnt->leaf++;
             while (true)
             {
+                if (COUNT) cnt->tri++;
                 const float4 *q = bvh.slots + 3 * (size_t)slot;
                 const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2);
                 float t, u, v;

@@ -83,7 +83,7 @@ int flx_create(flx_ctx **out, int device, uint32_t num_tasks, void *cuda_stream)
         ctx->st.lastSpecular = s; ctx->st.shadowBlocked = s + N; ctx->st.logicFlags = s + 2 * N; ctx->st.lastPickProb = (float *)(s + 3 * N);
     }
     // queues + counters + cursors + totals
-    const size_t queueBytes = FLX_NUM_QUEUES * N * 4 + 256;
+    const size_t queueBytes = FLX_NUM_QUEUES * N * 4 + 512;
     CREATE_CUDA(cudaMalloc(&ctx->queueBlock, queueBytes));
     CREATE_CUDA(cudaMemsetAsync(ctx->queueBlock, 0, queueBytes, ctx->stream));
     {
@@ -93,6 +93,7 @@ int flx_create(flx_ctx **out, int device, uint32_t num_tasks, void *cuda_stream)
         ctx->qs.counters = (flx_queue_counters *)tail;       // 40 B
         ctx->dPixelIdx = (uint32_t *)(tail + 64);            // pixel cursor + 2 work cursors
         ctx->dTotals = (RenderTotals *)(tail + 128);         // 48 B
+        ctx->dTraceStats = (unsigned long long *)(tail + 256); // 20 x u64
     }
     CREATE_CUDA(cudaMallocHost(&ctx->hCounters, 64 * sizeof(flx_queue_counters)));
     CREATE_CUDA(cudaStreamSynchronize(ctx->stream));

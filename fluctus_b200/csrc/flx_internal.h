@@ -110,6 +110,9 @@ struct flx_ctx
 
     // timing
     bool timing = false; StageTimer timers[6];
+    // visit counters of the COUNT=true trace kernels: 4 groups (ext, shadow, batch closest, batch any)
+    // x {inner, leaf, tri, hits, rays}
+    bool counting = false; unsigned long long *dTraceStats = nullptr;
 
     // scratch for the host-buffer ray-cast entry points
     void *dScratch = nullptr; size_t scratchBytes = 0;

@@ -130,7 +130,13 @@ uint64_t flx_launch_count(flx_ctx *ctx);          /* kernels launched by this co
  * clcontext.cpp:691-719).  enable != 0 starts recording; flx_get_kernel_time returns accumulated
  * milliseconds and launch counts per stage id (0 ext, 1 shadow, 2 logic, 3 raygen, 4 materials). */
 int flx_enable_timing(flx_ctx *ctx, int enable);
-int flx_get_kernel_time(flx_ctx *ctx, int stage, double *ms, uint64_t *launches);
+int flx_get_kernel_time(flx_ctx *ctx, int stage, double *ms, uint64_t *launches); /* stage 5 = ray batch */
+/* Visit counters of the traversal kernels, for the algorithmic-bytes roofline figure (the oracle
+ * counts the same quantities under the reference visit order).  While enabled, instrumented
+ * kernel variants run — never time those.  out = 4 groups {ext, shadow, batch closest, batch any}
+ * x {inner-node visits, leaf visits, triangle tests, hits, rays}. */
+int flx_set_trace_counting(flx_ctx *ctx, int enable);
+int flx_get_trace_counters(flx_ctx *ctx, uint64_t out[20]);
 
 #ifdef __cplusplus
 }

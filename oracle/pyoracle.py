@@ -205,6 +205,16 @@ def ref_host():
         for n in ("refh_tris", "refh_materials", "refh_nodes", "refh_indices"):
             getattr(R, n).restype = V
         R.refh_material_types.restype = C.c_uint
+        for n in ("refh_num_tris", "refh_num_materials", "refh_num_textures", "refh_num_nodes", "refh_num_indices",
+                  "refh_tris", "refh_materials", "refh_nodes", "refh_indices", "refh_material_types",
+                  "refh_scene_free", "refh_build_sbvh"):
+            getattr(R, n).argtypes = [V]
+        R.refh_scene_load.argtypes = [V, C.c_char_p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int]
+        R.refh_build_bvh.argtypes = [V, C.c_int]
+        R.refh_bounds.argtypes = [V, V, V]
+        R.refh_texture_info.argtypes = [V, C.c_size_t, C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.POINTER(V)]
+        R.refh_envmap_load.argtypes = [V, C.c_char_p]
+        R.refh_envmap_info.argtypes = [V, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(V), C.POINTER(V), C.POINTER(V), C.POINTER(V)]
         _REF = R
     return _REF
 

@@ -1,0 +1,240 @@
+"""Stage-by-stage parity of the CUDA wavefront kernels against the CPU oracle.
+
+For every stage the oracle's PRE-stage state, queues, counters and frame buffers are imported into
+the CUDA context (flx_import_state / flx_write_queue / flx_set_counters / flx_write_pixels), the
+stage runs once on each side, and the POST-stage state is compared per named field of the
+reference's GPUTaskState: integers exactly, floats within 1e-5 relative (north_star tolerance).
+Queues are compared as sets — slot order comes from atomics and is unspecified in the reference
+too.  libm ulps (sinf/cosf/atan2f/acosf/powf) can flip a `rand() < F` branch for a handful of
+paths; those are counted separately and bounded."""
+import numpy as np
+import pytest
+
+from conftest import cached_scene
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-5          # stated tolerance for floating-point path state
+MAX_FLIP_FRACTION = 2e-3  # paths allowed to diverge through a flipped comparison
+
+
+def _setup(oracle, scene, env, N, W, H, **kw):
+    from fluctus_b200 import CudaContext, abi, scene as fs
+    p = abi.make_render_params(W, H, n_tris=len(scene["tris"]), world_radius=fs.world_radius(scene), **kw)
+    wf = oracle.OracleWavefront(N, W, H)
+    wf.set_scene(scene)
+    ctx = CudaContext(num_tasks=N)
+    ctx.uploadSceneData(scene)
+    if env is not None:
+        wf.set_envmap(env)
+        ctx.createEnvMap(env)
+    wf.set_params(p.tobytes())
+    ctx.updateParams(p)
+    return wf, ctx, p
+
+
+def _push_oracle_to_gpu(wf, ctx):
+    from fluctus_b200 import abi
+    from fluctus_b200.context import BUF_PIXELS, BUF_SPP, BUF_DENOISER_ALBEDO, BUF_DENOISER_NORMAL
+    ctx.importState(wf.state())
+    cnt = wf.counters()
+    for qi, name in enumerate(abi.QUEUES):
+        n = int(cnt[name + "Queue"])
+        if n:
+            ctx.writeQueue(qi, wf.queue(qi)[:n])
+    ctx.setCounters(np.array([cnt]))
+    ctx.writePixels(BUF_PIXELS, wf.pixels())
+    ctx.writePixels(BUF_SPP, wf.spp())
+    ctx.writePixels(BUF_DENOISER_ALBEDO, wf.denoiser_albedo())
+    ctx.writePixels(BUF_DENOISER_NORMAL, wf.denoiser_normal())
+    ctx.setPixelIndex(wf.get_pixel_index())
+
+
+def _compare_state(gpu64, ref64, fields, what, allow_flips=True):
+    from fluctus_b200 import abi
+    N = ref64.shape[1]
+    bad = np.zeros(N, bool)
+    for name in fields:
+        g, r = abi.state_field(gpu64, name), abi.state_field(ref64, name)
+        if name in abi.INT_SLOTS:
+            bad |= (g != r) if g.ndim == 1 else (g != r).any(1)
+        else:
+            g64, r64 = g.astype(np.float64), r.astype(np.float64)
+            both_nan = np.isnan(g64) & np.isnan(r64)
+            same_inf = np.isinf(g64) & (g64 == r64)
+            with np.errstate(invalid="ignore"):
+                ok = (np.abs(g64 - r64) <= REL_TOL * np.maximum(np.abs(r64), 1e-3)) | both_nan | same_inf
+            bad |= ~ok if ok.ndim == 1 else ~ok.all(1)
+    frac = bad.mean()
+    limit = MAX_FLIP_FRACTION if allow_flips else 0.0
+    assert frac <= limit, "%s: %d of %d paths differ (fields %s)" % (what, bad.sum(), N, fields)
+    return bad
+
+
+def _compare_queues(ctx, wf, names, what):
+    from fluctus_b200 import abi
+    g, r = ctx.getCounters(), wf.counters()
+    for name in names:
+        ng, nr = int(g[name + "Queue"]), int(r[name + "Queue"])
+        qg = set(ctx.readQueue(name, ng).tolist()) if ng else set()
+        qr = set(wf.queue(abi.QUEUES.index(name))[:nr].tolist())
+        assert len(qg) == ng, "%s: duplicate entries in %s queue" % (what, name)
+        diff = len(qg ^ qr)
+        assert diff <= max(2, MAX_FLIP_FRACTION * wf.N), "%s: %s queue differs in %d entries (%d vs %d)" % (what, name, diff, ng, nr)
+
+
+ALL_FIELDS = ["orig", "dir", "shadowOrig", "shadowDir", "T", "Ei", "lastBsdf", "lastEmission", "lastT", "P", "N", "uvTex",
+              "lastPdfW", "pathLen", "seed", "lastSpecular", "shadowRayBlocked", "backfaceHit", "pixelIndex",
+              "firstDiffuseHit", "lastPdfDirect", "lastPdfImplicit", "lastCosTh", "lastLightPickProb", "shadowRayLen",
+              "t", "i", "areaLightHit", "matId"]
+HIT_FIELDS = ["P", "N", "uvTex", "t", "i", "areaLightHit", "matId", "pathLen"]
+
+
+def _run_lockstep(oracle, scene, env, N, W, H, iterations, **kw):
+    """Oracle drives; before each stage its state is pushed to the GPU, both run the stage, results compared."""
+    from fluctus_b200.context import BUF_PIXELS, BUF_SPP
+    wf, ctx, p = _setup(oracle, scene, env, N, W, H, **kw)
+    oracle.set_threads(1)
+    try:
+        # reset is compared from the natural (zero) initial state
+        wf.reset(); ctx.enqueueWfResetKernel()
+        _compare_state(ctx.exportState(), wf.state(), ALL_FIELDS, "reset", allow_flips=False)
+        _compare_queues(ctx, wf, ["raygen"], "reset")
+        wf.clear_queues(); ctx.enqueueClearWfQueues()
+        for it in range(iterations):
+            tag = "iter %d " % it
+            _push_oracle_to_gpu(wf, ctx)
+            wf.logic(False); ctx.enqueueWfLogicKernel(firstIteration=False)
+            _compare_state(ctx.exportState(), wf.state(), ALL_FIELDS, tag + "logic")
+            _compare_queues(ctx, wf, ["raygen", "shadow", "diffuse", "glossy", "ggxRefl", "ggxRefr", "delta", "emissive"], tag + "logic")
+            px_g, px_r = ctx.readPixels(BUF_PIXELS), wf.pixels()
+            # splat: same samples in a different atomic order -> tiny float reassociation only
+            assert np.allclose(px_g, px_r, rtol=1e-4, atol=1e-4), tag + "splat"
+            assert abs(float(px_g[:, 3].sum()) - float(px_r[:, 3].sum())) <= max(2, MAX_FLIP_FRACTION * N)
+            if int(p[0]["maxSpp"]) > 0:
+                assert np.abs(ctx.readPixels(BUF_SPP).astype(np.int64) - wf.spp().astype(np.int64)).max() <= 1
+                assert abs(int(ctx.getCounters()["splattedSamples"]) - int(wf.counters()["splattedSamples"])) <= max(2, MAX_FLIP_FRACTION * N)
+
+            _push_oracle_to_gpu(wf, ctx)
+            wf.raygen(); ctx.enqueueWfRaygenKernel()
+            _compare_state(ctx.exportState(), wf.state(), ALL_FIELDS, tag + "raygen")
+            _compare_queues(ctx, wf, ["extension"], tag + "raygen")
+
+            _push_oracle_to_gpu(wf, ctx)
+            wf.materials(); ctx.enqueueWfMaterialKernels()
+            _compare_state(ctx.exportState(), wf.state(), ALL_FIELDS, tag + "materials")
+            _compare_queues(ctx, wf, ["extension"], tag + "materials")
+
+            _push_oracle_to_gpu(wf, ctx)
+            wf.ext(); ctx.enqueueWfExtRayKernel()
+            # traversal is bit-exact: no tolerance, no flips
+            g, r = ctx.exportState(), wf.state()
+            _compare_state(g, r, HIT_FIELDS, tag + "ext", allow_flips=False)
+            from fluctus_b200 import abi
+            for f in ("P", "N", "uvTex", "t"):
+                assert np.array_equal(abi.state_field(g, f).view(np.uint32), abi.state_field(r, f).view(np.uint32)), tag + "ext bits " + f
+
+            _push_oracle_to_gpu(wf, ctx)
+            wf.shadow(); ctx.enqueueWfShadowRayKernel()
+            _compare_state(ctx.exportState(), wf.state(), ["shadowRayBlocked"], tag + "shadow", allow_flips=False)
+
+            cnt = wf.counters().copy()
+            wf.clear_queues(); ctx.enqueueClearWfQueues()
+            wf.update_pixel_index(int(cnt["raygenQueue"]))
+        return wf, ctx
+    finally:
+        oracle.set_threads(oracle.max_threads())
+
+
+def test_teapot_envmap_mis(oracle, teapot, night_env):
+    """cfg1-like: teapot + night.hdr, env-map MIS, no area light, N < pixels."""
+    wf, ctx = _run_lockstep(oracle, teapot, night_env, 4096, 96, 64, 7, max_bounces=4, use_env_map=True, use_area_light=False)
+    ctx.close()
+
+
+def test_teapot_area_light_roulette_dof(oracle, teapot):
+    """area light only, Russian roulette on, thin-lens camera, N > pixels."""
+    wf, ctx = _run_lockstep(oracle, teapot, None, 4096, 48, 48, 9, max_bounces=0, use_env_map=False, use_area_light=True,
+                            use_roulette=True, aperture=0.01, focal_dist=3.0, light_pos=(1.5, 1.5, 0.5))
+    ctx.close()
+
+
+def test_teapot_both_lights_check_spp(oracle, teapot, night_env):
+    """env map + area light (pick probability 0.5), CHECK_SPP cap, separate material queues."""
+    wf, ctx = _run_lockstep(oracle, teapot, night_env, 4096, 32, 32, 8, max_bounces=3, max_spp=2, use_env_map=True,
+                            use_area_light=True, separate_queues=True)
+    ctx.close()
+
+
+@pytest.mark.parametrize("separate", [False, True])
+def test_material_mix(oracle, night_env, separate):
+    """All BxDF classes in one scene: psor-cube geometry with its four materials re-typed to glossy,
+    rough dielectric, mirror, ideal dielectric / rough reflection / emissive / diffuse by triangle id."""
+    from fluctus_b200 import abi
+    base = cached_scene("psor_cube")
+    scene = dict(base)
+    mats = np.tile(base["materials"][:1], 8)
+    types = [abi.BXDF_DIFFUSE, abi.BXDF_GLOSSY, abi.BXDF_GGX_ROUGH_REFLECTION, abi.BXDF_IDEAL_REFLECTION,
+             abi.BXDF_GGX_ROUGH_DIELECTRIC, abi.BXDF_IDEAL_DIELECTRIC, abi.BXDF_EMISSIVE, abi.BXDF_MIXED]
+    for k, t in enumerate(types):
+        mats[k]["type"] = t
+        mats[k]["Kd"][:3] = (0.7, 0.5 + 0.05 * k, 0.3)
+        mats[k]["Ks"][:3] = (0.9, 0.8, 0.7) if k != 1 else (0.0, 0.0, 0.0)
+        mats[k]["Ke"][:3] = (2.0, 2.0, 2.0) if t == abi.BXDF_EMISSIVE else (0.0, 0.0, 0.0)
+        mats[k]["Ns"] = 0.15 + 0.05 * k
+        mats[k]["Ni"] = 1.5 if k != 1 else 0.0
+    tris = base["tris"].copy()
+    tris["matId"] = (np.arange(len(tris)) // 64) % 8
+    scene.update(materials=mats, tris=tris)
+    b = base["bounds"]
+    c = 0.5 * (b[0] + b[1])
+    cam = (float(c[0]), float(c[1]), float(b[1][2] + 1.2 * (b[1][2] - b[0][2])))
+    wf, ctx = _run_lockstep(oracle, scene, night_env, 8192, 64, 64, 8, max_bounces=6, use_env_map=True, use_area_light=True,
+                            separate_queues=separate, cam_pos=cam, light_pos=(float(c[0]) + 2.0, float(b[1][1]) + 1.0, float(c[2])))
+    ctx.close()
+
+
+def test_textured_scene_denoiser_aov(oracle, egyptcat, night_env):
+    """egyptcat: textured glossy + diffuse materials (albedo gamma, nearest/repeat lookup), AOV accumulation."""
+    from fluctus_b200.context import BUF_DENOISER_ALBEDO, BUF_DENOISER_NORMAL
+    from fluctus_b200 import CudaContext
+    b = egyptcat["bounds"]
+    c = 0.5 * (b[0] + b[1])
+    cam = (float(c[0]), float(c[1]), float(b[1][2] + 1.5 * (b[1][2] - b[0][2])))
+    # AOVs need the option on both sides before the lock-step run
+    orig_setup = globals()["_setup"]
+
+    def setup_with_aov(*a, **kw):
+        wf, ctx, p = orig_setup(*a, **kw)
+        wf.set_options(denoiser_aov=True)
+        ctx.setOptions(denoiser_aov=True)
+        return wf, ctx, p
+    globals()["_setup"] = setup_with_aov
+    try:
+        wf, ctx = _run_lockstep(oracle, egyptcat, night_env, 4096, 64, 64, 5, max_bounces=4, use_env_map=True,
+                                use_area_light=False, cam_pos=cam)
+    finally:
+        globals()["_setup"] = orig_setup
+    assert np.allclose(ctx.readPixels(BUF_DENOISER_ALBEDO), wf.denoiser_albedo(), rtol=1e-4, atol=1e-4)
+    assert np.allclose(ctx.readPixels(BUF_DENOISER_NORMAL), wf.denoiser_normal(), rtol=1e-4, atol=1e-4)
+    ctx.close()
+
+
+def test_postprocess_operators(oracle, teapot):
+    from fluctus_b200 import CudaContext, abi
+    from fluctus_b200.context import BUF_PIXELS, BUF_PREVIEW
+    W, H = 40, 25
+    rng = np.random.default_rng(0)
+    px = rng.uniform(0, 30, (W * H, 4)).astype(np.float32)
+    px[:, 3] = rng.integers(0, 9, W * H)
+    for op in (0, 1, 2, 3):
+        p = abi.make_render_params(W, H, tonemap=op, exposure=1.7)
+        wf = oracle.OracleWavefront(64, W, H)
+        wf.set_params(p.tobytes())
+        wf.pixels()[:] = px
+        ctx = CudaContext(num_tasks=64)
+        ctx.updateParams(p)
+        ctx.writePixels(BUF_PIXELS, px)
+        ctx.enqueuePostprocessKernel()
+        assert np.allclose(ctx.readPixels(BUF_PREVIEW), wf.postprocess(), rtol=1e-5, atol=1e-6), op
+        ctx.close()

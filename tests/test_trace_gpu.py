@@ -1,0 +1,128 @@
+"""Closest-hit / any-hit parity of the CUDA traversal kernels against the CPU oracle, through the
+C-ABI (flx_trace_closest / flx_trace_any).  Contract (BASELINE.json north_star): hit index and
+hit/miss bit-exact; we also require hit.t, P, N, uv bit-exact because the arithmetic is op-for-op
+the reference's (no FMA, IEEE div/sqrt)."""
+import numpy as np
+import pytest
+
+from conftest import bits, cached_scene
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from fluctus_b200 import CudaContext
+    c = CudaContext(num_tasks=4096)
+    yield c
+    c.close()
+
+
+def _rays_inside(scene, n, seed):
+    """Rays that start inside the scene box (many hits, deep traversals), with finite tmax for some."""
+    rng = np.random.default_rng(seed)
+    b = scene["bounds"]
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, :3] = rng.uniform(b[0], b[1], (n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    rays[:, 4:7] = d
+    rays[:, 3] = np.float32(3.402823466e+38)
+    return rays
+
+
+def _check_closest(ctx, oracle, scene, rays):
+    ctx.uploadSceneData(scene)
+    ref = oracle.trace_closest(scene, rays, 0, want_hits=True)
+    hit_i, hit_t, hits = ctx.traceClosest(rays, want_hits=True)
+    assert np.array_equal(hit_i, ref["hit_i"])
+    assert np.array_equal(bits(hit_t), bits(ref["hit_t"]))
+    for f in ("P", "N", "uv", "t"):
+        assert np.array_equal(bits(hits[f]), bits(ref["hits"][f])), f
+    for f in ("i", "matId", "areaLightHit"):
+        assert np.array_equal(hits[f], ref["hits"][f]), f
+    # the index-only path (no attribute fetch) must agree too
+    hit_i2, hit_t2 = ctx.traceClosest(rays)
+    assert np.array_equal(hit_i2, hit_i) and np.array_equal(bits(hit_t2), bits(hit_t))
+    return ref
+
+
+def test_closest_teapot_incoherent(ctx, oracle, teapot):
+    from fluctus_b200 import scene as fs
+    rays = fs.bench_rays(1 << 17, teapot["bounds"])
+    ref = _check_closest(ctx, oracle, teapot, rays)
+    assert 0.1 < (ref["hit_i"] >= 0).mean() < 0.4
+
+
+def test_closest_teapot_inside(ctx, oracle, teapot):
+    _check_closest(ctx, oracle, teapot, _rays_inside(teapot, 1 << 16, 1))
+
+
+def test_closest_axis_aligned_and_degenerate_rays(ctx, oracle, teapot):
+    """Zero direction components give +-inf reciprocals and 0*inf = NaN in the slab test
+    (src/intersect.cl:43-50): fmin/fmax must drop the NaN exactly as OpenCL does."""
+    rays = _rays_inside(teapot, 6 * 512, 2)
+    for k, axis in enumerate(("x+", "x-", "y+", "y-", "z+", "z-")):
+        d = np.zeros(3, np.float32)
+        d[k // 2] = 1.0 if k % 2 == 0 else -1.0
+        rays[k * 512:(k + 1) * 512, 4:7] = d
+    rays[:64, 4:7] = 0.0                    # null direction (what an emissive hit produces)
+    rays[64:128, 3] = 0.05                  # short tmax
+    rays[128:192, 3] = 0.0                  # tmax = 0: nothing can be closer
+    rays[192:200, 0] = np.nan               # NaN origin must come back as a miss
+    _check_closest(ctx, oracle, teapot, rays)
+
+
+def test_any_hit_matches_oracle(ctx, oracle, teapot):
+    rays = _rays_inside(teapot, 1 << 15, 3)
+    rays[:, 3] = np.random.default_rng(4).uniform(0.01, 1.5, len(rays)).astype(np.float32)
+    ctx.uploadSceneData(teapot)
+    assert np.array_equal(ctx.traceAny(rays), oracle.trace_any(teapot, rays, 0))
+
+
+def test_replicated_grid(ctx, oracle, teapot):
+    """Instanced teapots: exact-t ties between distinct triangles never occur across instances, SBVH
+    duplicates inside one do; the visit order must resolve them like the reference."""
+    from fluctus_b200 import scene as fs
+    grid = fs.replicate_grid(teapot, (3, 2, 2), (2.2, 1.1, 1.4))
+    assert len(grid["tris"]) == 12 * len(teapot["tris"])
+    rays = fs.bench_rays(1 << 16, grid["bounds"])
+    ref = _check_closest(ctx, oracle, grid, rays)
+    assert (ref["hit_i"] >= 0).mean() > 0.2
+    # bit-stack traversal of the oracle walks the same order (SURVEY §4 consistency pair 1)
+    alt = oracle.trace_closest(grid, rays, 1)
+    assert np.array_equal(alt["hit_i"], ref["hit_i"])
+
+
+@pytest.mark.parametrize("name", ["egyptcat", "psor_cube"])
+def test_closest_reference_assets(ctx, oracle, name):
+    scene = cached_scene(name)
+    rays = _rays_inside(scene, 1 << 15, 5)
+    _check_closest(ctx, oracle, scene, rays)
+
+
+def test_single_leaf_scene(ctx, oracle, teapot):
+    """A hierarchy whose root is a leaf (<= 8 triangles): the root reference itself is a leaf reference."""
+    from fluctus_b200.abi import NODE_DT
+    tris = teapot["tris"][:5].copy()
+    nodes = np.zeros(1, NODE_DT)
+    p = tris["v"][:, :, 0, :3].reshape(-1, 3)
+    nodes["bmin"][0, :3], nodes["bmax"][0, :3] = p.min(0), p.max(0)
+    nodes["parent"], nodes["iStartOrRight"], nodes["nPrims"] = -1, 0, 5
+    scene = dict(teapot, tris=tris, nodes=nodes, indices=np.arange(5, dtype=np.uint32))
+    scene["bounds"] = np.stack([p.min(0), p.max(0)])
+    rays = _rays_inside(scene, 4096, 6)
+    rays[:, :3] += np.float32(0.3) * np.random.default_rng(7).normal(size=(4096, 3)).astype(np.float32)
+    _check_closest(ctx, oracle, scene, rays)
+
+
+def test_empty_batch_and_errors(ctx, teapot):
+    from fluctus_b200 import FluctusError
+    ctx.uploadSceneData(teapot)
+    hit_i, hit_t = ctx.traceClosest(np.zeros((0, 8), np.float32))
+    assert len(hit_i) == 0
+    bad = dict(teapot, indices=teapot["indices"].copy())
+    bad["indices"][0] = len(teapot["tris"]) + 7
+    with pytest.raises(FluctusError):
+        ctx.uploadSceneData(bad)
+    ctx.uploadSceneData(teapot)  # context stays usable after a rejected upload
