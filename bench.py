@@ -1,0 +1,451 @@
+#!/usr/bin/env python
+"""bench.py — the headline measurement of the wavefront path-tracing hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json metric "Msamples/s (1080p kitchen, 8 bounces)", configs[3]): the kitchen
+stand-in scene (Country-Kitchen.obj is stripped from the reference snapshot, SURVEY.md §7.3.7;
+fluctus_b200/standin.py rebuilds a room with the kitchen's material mix from the committed teapot
+fixture), 1920x1080, 8 bounces, environment-map MIS + area light, NUM_TASKS = 2^20 paths per GPU.
+
+One STEP = one frame: reset, ITERS wavefront iterations (logic -> raygen -> materials -> ext ->
+shadow -> bookkeeping, the reference's benchmark inner loop, src/tracer.cpp:737-778), one
+all-reduce of the float accumulation buffer over the ranks, tonemap.  Per-GPU work is fixed as N
+grows (each rank traces its own N paths with rank-offset seeds): weak scaling.
+  value : Msamples/s, device-resident, CUDA events around K steps, max over ranks
+  e2e   : the same frame through the public API with host buffers: RenderParams uploaded and
+          the tonemapped frame + counters read back to pinned host memory inside the timed region
+  roofline : extension-ray traversal kernel (k_ext), algorithmic bytes of SURVEY.md §8(d) / DESIGN.md
+  cpu_baseline / --impl reference : the CPU restatement of the reference's OpenCL kernels
+          (oracle/, OpenMP over work-items) on the host cores — the reference's own device code
+          needs an OpenCL runtime that does not exist on this box.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+WIDTH, HEIGHT = 1920, 1080
+NUM_TASKS = 1 << 20
+MAX_BOUNCES = 8
+ITERS_PER_STEP = 48          # wavefront iterations per frame
+CPU_TASKS = 1 << 18          # path pool of the CPU arm (throughput per path does not depend on it)
+CPU_ITERS_PER_STEP = 2
+CPU_RAMP_ITERS = 14          # untimed iterations that bring the CPU pool to steady state
+METRIC = "Msamples/s (1080p kitchen, 8 bounces)"
+# algorithmic bytes of one extension-ray traversal
+B_RAY_IN, B_RAY_OUT, B_INNER, B_TRI, B_HIT = 28, 56, 56, 40, 64
+
+
+def load_workload():
+    from fluctus_b200 import scene as fs
+    from fluctus_b200.standin import kitchen_standin
+    teapot = fs.load_scene(os.path.join(GOLDEN, "teapot_sbvh.npz"))
+    env = fs.load_envmap(os.path.join(GOLDEN, "night_env.npz"))
+    scene, view = kitchen_standin(teapot)
+    settings = dict(max_bounces=MAX_BOUNCES, use_env_map=True, use_area_light=True, sample_implicit=True,
+                    sample_explicit=True, use_roulette=False, separate_queues=True, tonemap=2, **view)
+    return teapot, scene, env, settings
+
+
+def config_dict(n_gpus, scene, impl):
+    return {"workload": "kitchen stand-in (%d tris, kitchen material mix, textured floor), 1920x1080, 8 bounces, "
+                        "env-map MIS + area light" % len(scene["tris"]),
+            "num_tasks_per_gpu": NUM_TASKS if impl == "ours" else CPU_TASKS,
+            "iterations_per_step": ITERS_PER_STEP if impl == "ours" else CPU_ITERS_PER_STEP,
+            "step": "one frame: reset + iterations + all-reduce + tonemap" if impl == "ours"
+                    else "steady-state wavefront iterations on the CPU path pool",
+            "parallelism": "sample-sharded x%d, one all-reduce of the accumulation buffer per frame" % n_gpus,
+            "l2": "inputs larger than L2: 208 MB path state + 33 MB frame per pass (L2 126 MB)",
+            "stand_in_for": "assets/country_kitchen/Country-Kitchen.obj (stripped from the reference snapshot)"}
+
+
+# ---------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.thread = [], None, None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def window(self, t0, t1):
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        sm, mx, reasons, power = [], [], set(), []
+        for ts, line in self.rows:
+            if ts < t0 or ts > t1 + 0.15:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                "power_w_max": float(max(power)), "samples": len(sm)}
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+
+def measured_peak_gbs():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------------------------------
+# CPU arm: the oracle's restatement of the reference's .cl kernels, OpenMP over work-items
+class CpuWavefront:
+    def __init__(self, scene, env, settings):
+        from oracle import pyoracle  # allowed here: cpu_baseline / --impl reference legs only
+        from fluctus_b200 import abi, scene as fs
+        self.po = pyoracle
+        self.threads = pyoracle.max_threads()
+        pyoracle.set_threads(self.threads)
+        self.wf = pyoracle.OracleWavefront(CPU_TASKS, WIDTH, HEIGHT)
+        self.wf.set_scene(scene)
+        self.wf.set_envmap(env)
+        p = abi.make_render_params(WIDTH, HEIGHT, n_tris=len(scene["tris"]), world_radius=fs.world_radius(scene), **settings)
+        self.wf.set_params(p.tobytes())
+        self.wf.reset(); self.wf.clear_queues(); self.wf.set_pixel_index(0)
+        self.wf.raygen(); self.wf.ext()
+        self.first = True
+
+    def iterate(self, n):
+        """n passes of the benchmark inner loop (tracer.cpp:737-778); returns (samples, ext rays, shadow rays)."""
+        wf, s, e, sh = self.wf, 0, 0, 0
+        for _ in range(n):
+            wf.logic(False); wf.raygen(); wf.materials()
+            c = wf.counters().copy()
+            wf.ext(); wf.shadow(); wf.clear_queues()
+            wf.update_pixel_index(int(c["raygenQueue"]))
+            if not self.first:
+                s += int(c["raygenQueue"])
+            self.first = False
+            e += int(c["extensionQueue"]); sh += int(c["shadowQueue"])
+        return s, e, sh
+
+
+def cpu_baseline(scene, env, settings, budget_s=12.0):
+    cw = CpuWavefront(scene, env, settings)
+    cw.iterate(CPU_RAMP_ITERS)
+    t0 = time.perf_counter()
+    samples = rays = iters = 0
+    while True:
+        s, e, sh = cw.iterate(1)
+        samples += s; rays += e + sh; iters += 1
+        dt = time.perf_counter() - t0
+        if dt >= budget_s or iters >= 64:
+            break
+    return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": cw.threads, "kind": "port",
+            "mrays_per_s": rays / dt / 1e6,
+            "sample": "%d steady-state wavefront iterations of a %d-path pool (after %d untimed ramp-up iterations), "
+                      "same scene / resolution / params; %.1f s" % (iters, CPU_TASKS, CPU_RAMP_ITERS, dt)}
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's algorithm on the host cores (oracle port; the OpenCL device
+    code itself has no runtime here).  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    teapot, scene, env, settings = load_workload()
+    cw = CpuWavefront(scene, env, settings)
+    cw.iterate(CPU_RAMP_ITERS)
+    for _ in range(args.warmup):
+        cw.iterate(CPU_ITERS_PER_STEP)
+    t0 = time.perf_counter()
+    samples = 0
+    for _ in range(args.steps):
+        samples += cw.iterate(CPU_ITERS_PER_STEP)[0]
+    dt = time.perf_counter() - t0
+    val = samples / dt / 1e6
+    sample = ("%d steps x %d steady-state iterations of a %d-path pool after %d ramp-up iterations"
+              % (args.steps, CPU_ITERS_PER_STEP, CPU_TASKS, CPU_RAMP_ITERS))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "Msamples/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict(args.gpus, scene, "reference"),
+        "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": cw.threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPU arm
+def traversal_bytes(cnt, rays=None):
+    """Algorithmic bytes of SURVEY.md §8(d) for `rays` rays with the per-ray visit statistics of cnt."""
+    r = max(int(cnt["rays"]), 1)
+    per_ray = (B_RAY_IN + B_RAY_OUT) + (cnt["inner"] * B_INNER + cnt["tri"] * B_TRI + cnt["hits"] * B_HIT) / r
+    return per_ray * (r if rays is None else rays), per_ray
+
+
+def run_raycast(dev, rank, world, teapot, peak_gbs, steps, warmup, check):
+    """cfg5: 2^24 incoherent rays against the 15x15x14 replicated-teapot SBVH (10.1 M triangles)."""
+    import torch
+    from fluctus_b200 import CudaContext, scene as fs
+    from fluctus_b200.context import STAGE_TRACE_BATCH
+    from fluctus_b200.multi_gpu import split_rays
+    t_build = time.perf_counter()
+    grid = fs.replicate_grid(teapot, (15, 15, 14), (2.2, 1.1, 1.4))
+    n_total = 1 << 24
+    first, n = split_rays(n_total, rank, world)
+    rays = fs.bench_rays(n, grid["bounds"], first=first)
+    stream = torch.cuda.current_stream(dev)
+    ctx = CudaContext(num_tasks=1024, device=dev.index, stream=stream.cuda_stream)
+    ctx.uploadSceneData(grid)
+    t_build = time.perf_counter() - t_build
+    d_rays = torch.from_numpy(rays).to(dev)
+    d_i = torch.empty(n, dtype=torch.int32, device=dev)
+    d_t = torch.empty(n, dtype=torch.float32, device=dev)
+    h_rays = torch.from_numpy(rays).pin_memory()
+    h_i = torch.empty(n, dtype=torch.int32).pin_memory()
+    h_t = torch.empty(n, dtype=torch.float32).pin_memory()
+
+    def device_pass():
+        ctx.traceClosestDevice(d_rays.data_ptr(), n, d_i.data_ptr(), d_t.data_ptr())
+
+    def host_pass():  # public host-buffer entry: H2D rays, trace, D2H hit index + distance, synchronises
+        ctx._check(ctx.L.flx_trace_closest(ctx.h, h_rays.data_ptr(), n, h_i.data_ptr(), h_t.data_ptr(), None))
+
+    out = {}
+    for name, fn in (("device", device_pass), ("host", host_pass)):
+        for _ in range(max(warmup, 3)):
+            fn()
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            torch.distributed.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        if name == "device":
+            ctx.enableTiming(True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            torch.distributed.all_reduce(ms, op=torch.distributed.ReduceOp.MAX)
+        out[name] = float(ms.item()) / steps
+        if name == "device":
+            k_ms, k_n = ctx.kernelTime(STAGE_TRACE_BATCH)
+            ctx.enableTiming(False)
+            out["kernel_ms"] = k_ms / max(k_n, 1)
+    # visit statistics from the instrumented kernel variant (untimed)
+    ctx.setTraceCounting(True)
+    device_pass()
+    cnt = ctx.traceCounters()["batch_closest"]
+    ctx.setTraceCounting(False)
+    # microbench variant of the §8(d) formula: 32 B in, 8 B out per ray
+    per_ray = 40 + (cnt["inner"] * B_INNER + cnt["tri"] * B_TRI) / max(cnt["rays"], 1)
+    achieved = per_ray * n / (out["kernel_ms"] * 1e-3) / 1e9
+    res = {"metric": "incoherent Mrays/s (2^24 rays vs replicated-teapot SBVH, closest hit)",
+           "value": n_total / (out["device"] * 1e-3) / 1e6, "unit": "Mrays/s",
+           "e2e": {"value": n_total / (out["host"] * 1e-3) / 1e6, "unit": "Mrays/s",
+                   "h2d_bytes_per_step": 32 * n, "d2h_bytes_per_step": 8 * n},
+           "rays": n_total, "triangles": int(len(grid["tris"])), "nodes": int(len(grid["nodes"])),
+           "scene_build_upload_s": round(t_build, 1),
+           "per_ray": {"inner_nodes": cnt["inner"] / max(cnt["rays"], 1), "triangle_tests": cnt["tri"] / max(cnt["rays"], 1),
+                       "hit_fraction": cnt["hits"] / max(cnt["rays"], 1), "algorithmic_bytes": per_ray},
+           "roofline": {"bound": "hbm", "kernel": "k_trace_batch", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
+                        "frac": achieved / peak_gbs, "traffic": None, "kernel_ms": out["kernel_ms"]}}
+    if check and rank == 0:  # spot parity against the oracle (checker only; tests/ hold the full comparison)
+        from oracle import pyoracle
+        m = 1 << 15
+        ref = pyoracle.trace_closest(grid, rays[:m], 0)
+        gi, gt = d_i[:m].cpu().numpy(), d_t[:m].cpu().numpy()
+        res["parity"] = {"rays_checked": m, "hit_i_equal": bool(np.array_equal(gi, ref["hit_i"])),
+                         "hit_t_bits_equal": bool(np.array_equal(gt.view(np.uint32), ref["hit_t"].view(np.uint32)))}
+    ctx.close()
+    return res
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import fluctus_b200 as fx
+    from fluctus_b200.context import BUF_PREVIEW, STAGE_EXT, STAGE_SHADOW, STAGE_LOGIC, STAGE_RAYGEN, STAGE_MATERIALS
+    from fluctus_b200.multi_gpu import allreduce_pixels, pixels_tensor
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — this backend has no CPU fallback (use --impl reference for the CPU arm)")
+    fx.load()  # fails loudly when libfluctus_cuda.so is missing
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)  # the context, torch events and NCCL all order on this stream
+
+    teapot, scene, env, settings = load_workload()
+    tr = fx.Tracer(WIDTH, HEIGHT, num_tasks=NUM_TASKS, device=local, rank=rank, world_size=world,
+                   stream=stream.cuda_stream, **settings)
+    tr.init(scene, env)
+    c = tr.clctx
+    pix = pixels_tensor(c, dev)
+    cursor0 = tr._cursor_start()
+    n_px = WIDTH * HEIGHT
+    h_frame = torch.empty((n_px, 4), dtype=torch.float32).pin_memory()
+    h_frame_np = h_frame.numpy()
+
+    def frame(host_io):
+        if host_io:
+            c.updateParams(tr.params)              # the frame's inputs: 256-byte RenderParams from the host
+        c.setPixelIndex(0)
+        c.render(0, reset=True)                    # reset + clear + priming raygen + ext
+        c.setPixelIndex(cursor0)
+        c.render(ITERS_PER_STEP)
+        tot = None
+        if world > 1:
+            tot = c.getRenderTotals()              # before the reduce: totals are per rank
+            allreduce_pixels(pix)                  # ONE all-reduce of the accumulation buffer per frame
+        c.enqueuePostprocessKernel()
+        if host_io:
+            c.readPixels(BUF_PREVIEW, out=h_frame_np)  # tonemapped frame -> pinned host memory (synchronises)
+        return tot if tot is not None else c.getRenderTotals()
+
+    def timed(host_io, steps, with_events):
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        if with_events:
+            c.enableTiming(True)
+        l0 = c.launchCount()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        e0.record(stream)
+        tot = dict(samples=0, extension=0, shadow=0, primary=0)
+        for _ in range(steps):
+            t = frame(host_io)
+            for k in tot:
+                tot[k] += t[k]
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        t1 = time.time()
+        if world > 1:
+            dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        agg = torch.tensor([tot["samples"], tot["extension"], tot["shadow"], tot["primary"]], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(agg, op=dist.ReduceOp.SUM)
+        stage = None
+        if with_events:
+            stage = {n: c.kernelTime(s) for n, s in (("ext", STAGE_EXT), ("shadow", STAGE_SHADOW), ("logic", STAGE_LOGIC),
+                                                     ("raygen", STAGE_RAYGEN), ("materials", STAGE_MATERIALS))}
+            c.enableTiming(False)
+        return dict(ms=float(ms.item()), samples=float(agg[0]), ext=float(agg[1]), shadow=float(agg[2]), primary=float(agg[3]),
+                    local=tot, launches=c.launchCount() - l0, stage=stage, t0=t0, t1=t1)
+
+    clocks = ClockSampler(local) if rank == 0 else None
+    for _ in range(max(args.warmup, 1)):
+        frame(False)
+    r = timed(False, args.steps, True)          # device-resident, per-stage CUDA events inside the timed region
+    for _ in range(2):
+        frame(True)
+    h = timed(True, args.steps, False)          # end to end through the host-buffer API (graph replay)
+    clk = clocks.window(r["t0"], r["t1"]) if clocks else None
+    if clocks:
+        clocks.stop()
+
+    # visit statistics of the extension-ray kernel from the instrumented variant: one untimed frame
+    c.setTraceCounting(True)
+    frame(False)
+    cnt = c.traceCounters()
+    c.setTraceCounting(False)
+    peak, peak_src = measured_peak_gbs()
+    ext_ms, ext_n = r["stage"]["ext"]
+    ext_bytes, ext_per_ray = traversal_bytes(cnt["ext"], rays=r["local"]["extension"])
+    ext_achieved = ext_bytes / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+    stage_ms = {k: v[0] for k, v in r["stage"].items()}
+    stage_sum = sum(stage_ms.values())
+
+    raycast = None
+    if not args.no_raycast:
+        raycast = run_raycast(dev, rank, world, teapot, peak, max(args.steps // 2, 3), args.warmup, check=(world == 1))
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_baseline(scene, env, settings)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": r["samples"] / (r["ms"] * 1e-3) / 1e6, "unit": "Msamples/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms"] / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(world, scene, "ours"),
+            "mrays_per_s": {"extension": r["ext"] / (r["ms"] * 1e-3) / 1e6, "shadow": r["shadow"] / (r["ms"] * 1e-3) / 1e6,
+                            "total": (r["ext"] + r["shadow"]) / (r["ms"] * 1e-3) / 1e6},
+            "e2e": {"value": h["samples"] / (h["ms"] * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": h["ms"] / args.steps,
+                    "h2d_bytes_per_step": 256, "d2h_bytes_per_step": n_px * 16 + 48},
+            "gpu_launches": int(r["launches"]),
+            "roofline": {"bound": "hbm", "kernel": "k_ext (extension-ray closest-hit traversal)", "achieved": ext_achieved,
+                         "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": ext_achieved / peak, "traffic": None,
+                         "launches": int(ext_n), "avg_launch_ms": ext_ms / max(ext_n, 1),
+                         "algorithmic_bytes_per_ray": ext_per_ray,
+                         "share_of_step": ext_ms / stage_sum if stage_sum else None},
+            "stage_ms_per_step": {k: v / args.steps for k, v in stage_ms.items()},
+            "clocks": clk, "cpu_baseline": cpu, "raycast": raycast,
+        }
+        print(json.dumps(line))
+    tr.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
+    ap.add_argument("--no-raycast", action="store_true", help="skip the cfg5 ray-cast microbench")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

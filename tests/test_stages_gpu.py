@@ -90,7 +90,7 @@ ALL_FIELDS = ["orig", "dir", "shadowOrig", "shadowDir", "T", "Ei", "lastBsdf", "
 HIT_FIELDS = ["P", "N", "uvTex", "t", "i", "areaLightHit", "matId", "pathLen"]
 
 
-def _run_lockstep(oracle, scene, env, N, W, H, iterations, **kw):
+def _run_lockstep(oracle, scene, env, N, W, H, iterations, prime=False, **kw):
     """Oracle drives; before each stage its state is pushed to the GPU, both run the stage, results compared."""
     from fluctus_b200.context import BUF_PIXELS, BUF_SPP
     wf, ctx, p = _setup(oracle, scene, env, N, W, H, **kw)
@@ -100,7 +100,22 @@ def _run_lockstep(oracle, scene, env, N, W, H, iterations, **kw):
         wf.reset(); ctx.enqueueWfResetKernel()
         _compare_state(ctx.exportState(), wf.state(), ALL_FIELDS, "reset", allow_flips=False)
         _compare_queues(ctx, wf, ["raygen"], "reset")
-        wf.clear_queues(); ctx.enqueueClearWfQueues()
+        if prime:
+            # Tracer::update order (tracer.cpp:263-268): reset -> raygen -> ext -> clear, so that the first
+            # logic pass sees real primary hits.  Without it (runBenchmarkFromFile order, tracer.cpp:633-645:
+            # reset -> clear) every path enters logic with pathLen 0 and pixelIndex 0, and under CHECK_SPP
+            # they all race on samplesPerPixel[0] — schedule-dependent in the reference as well.
+            _push_oracle_to_gpu(wf, ctx)
+            wf.raygen(); ctx.enqueueWfRaygenKernel()
+            _compare_state(ctx.exportState(), wf.state(), ALL_FIELDS, "prime raygen")
+            _push_oracle_to_gpu(wf, ctx)
+            wf.ext(); ctx.enqueueWfExtRayKernel()
+            _compare_state(ctx.exportState(), wf.state(), HIT_FIELDS, "prime ext", allow_flips=False)
+            cnt0 = wf.counters().copy()
+            wf.clear_queues(); ctx.enqueueClearWfQueues()
+            wf.update_pixel_index(int(cnt0["raygenQueue"]))
+        else:
+            wf.clear_queues(); ctx.enqueueClearWfQueues()
         for it in range(iterations):
             tag = "iter %d " % it
             _push_oracle_to_gpu(wf, ctx)
@@ -161,7 +176,9 @@ def test_teapot_area_light_roulette_dof(oracle, teapot):
 
 def test_teapot_both_lights_check_spp(oracle, teapot, night_env):
     """env map + area light (pick probability 0.5), CHECK_SPP cap, separate material queues."""
-    wf, ctx = _run_lockstep(oracle, teapot, night_env, 4096, 32, 32, 8, max_bounces=3, max_spp=2, use_env_map=True,
+    # N == number of pixels and primed start: at most one path per pixel is in flight, so the CHECK_SPP
+    # counter has no intra-pass race and the serial oracle is a valid lock-step reference.
+    wf, ctx = _run_lockstep(oracle, teapot, night_env, 4096, 64, 64, 10, prime=True, max_bounces=3, max_spp=2, use_env_map=True,
                             use_area_light=True, separate_queues=True)
     ctx.close()
 
