@@ -90,7 +90,7 @@ ALL_FIELDS = ["orig", "dir", "shadowOrig", "shadowDir", "T", "Ei", "lastBsdf", "
 HIT_FIELDS = ["P", "N", "uvTex", "t", "i", "areaLightHit", "matId", "pathLen"]
 
 
-def _run_lockstep(oracle, scene, env, N, W, H, iterations, prime=False, **kw):
+def _run_lockstep(oracle, scene, env, N, W, H, iterations, prime=False, spp_prefill=None, **kw):
     """Oracle drives; before each stage its state is pushed to the GPU, both run the stage, results compared."""
     from fluctus_b200.context import BUF_PIXELS, BUF_SPP
     wf, ctx, p = _setup(oracle, scene, env, N, W, H, **kw)
@@ -100,6 +100,8 @@ def _run_lockstep(oracle, scene, env, N, W, H, iterations, prime=False, **kw):
         wf.reset(); ctx.enqueueWfResetKernel()
         _compare_state(ctx.exportState(), wf.state(), ALL_FIELDS, "reset", allow_flips=False)
         _compare_queues(ctx, wf, ["raygen"], "reset")
+        if spp_prefill is not None:  # CHECK_SPP: start from a partly filled per-pixel sample counter
+            wf.spp()[:] = spp_prefill
         if prime:
             # Tracer::update order (tracer.cpp:263-268): reset -> raygen -> ext -> clear, so that the first
             # logic pass sees real primary hits.  Without it (runBenchmarkFromFile order, tracer.cpp:633-645:
@@ -176,10 +178,15 @@ def test_teapot_area_light_roulette_dof(oracle, teapot):
 
 def test_teapot_both_lights_check_spp(oracle, teapot, night_env):
     """env map + area light (pick probability 0.5), CHECK_SPP cap, separate material queues."""
-    # N == number of pixels and primed start: at most one path per pixel is in flight, so the CHECK_SPP
-    # counter has no intra-pass race and the serial oracle is a valid lock-step reference.
-    wf, ctx = _run_lockstep(oracle, teapot, night_env, 4096, 64, 64, 10, prime=True, max_bounces=3, max_spp=2, use_env_map=True,
-                            use_area_light=True, separate_queues=True)
+    # Two in-flight paths on the same pixel race on samplesPerPixel[pix] (in the reference as well), so the
+    # serial oracle is only a lock-step reference while every path owns its pixel: 256x128 pixels for 4096
+    # paths (the cursor cannot wrap within the run) and a primed start.  The cap itself is exercised by
+    # pre-filling the counter: a third of the pixels already full, a third one sample short.
+    W, H, spp = 256, 128, 2
+    fill = (np.arange(W * H) % 3 == 0) * spp + (np.arange(W * H) % 3 == 1) * (spp - 1)
+    wf, ctx = _run_lockstep(oracle, teapot, night_env, 4096, W, H, 7, prime=True, spp_prefill=fill.astype(np.uint32),
+                            max_bounces=3, max_spp=spp, use_env_map=True, use_area_light=True, separate_queues=True)
+    assert int(wf.counters()["splattedSamples"]) >= 0 and (wf.spp() <= spp).all()
     ctx.close()
 
 
