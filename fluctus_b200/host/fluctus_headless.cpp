@@ -1,0 +1,112 @@
+// fluctus_headless — headless render entry point of the B200 backend.
+//
+// Replaces the reference's `Fluctus -b` batch mode (reference src/main.cpp:20-140 + Tracer::renderSingle,
+// src/tracer.cpp:108-182), which cannot run without a GLFW window and an OpenCL-GL context.  The command line
+// keeps the reference's flags (-x -y -s -b scenes...) and its settings.json surface; rendering uses the
+// wavefront loop (the path this backend accelerates) instead of the microkernel renderer.
+//
+//   fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings settings.json] [--env map.hdr] [--bounces N]
+//                    [--iterations N] [--device D] [--out image.ppm|.pfm] [--save-scene out.flxs] scene...
+//
+// scene: a .flxs container (host_scene.hpp) or — when built against the reference tree — any file the
+// reference's Scene::loadModel understands (.obj .ply .pbrt .pbf .sc.json), loaded and SBVH-built by the
+// reference's own code.  Prints one JSON line per scene with the statistics the reference logs
+// (src/tracer.cpp:184-200, :441-444): primary / extension / shadow rays, samples, seconds, MRays/s.
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include "headless_tracer.hpp"
+
+static void usage()
+{
+    std::cerr << "usage: fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings FILE] [--env FILE.hdr] [--bounces N]\n"
+                 "                        [--iterations N] [--device D] [--out FILE.ppm|.pfm] [--save-scene FILE.flxs] scene...\n";
+}
+
+static bool endsWith(const std::string &s, const std::string &e) { return s.size() >= e.size() && s.compare(s.size() - e.size(), e.size(), e) == 0; }
+
+int main(int argc, char **argv)
+{
+    flx::Settings settings;
+    int width = -1, height = -1, spp = 32, device = 0, bounces = -1;
+    uint32_t iterations = 0;
+    std::string out = "output.ppm", saveScene, env;
+    std::vector<std::string> scenes;
+    try
+    {
+        for (int i = 1; i < argc; i++)
+        {
+            const std::string a = argv[i];
+            auto next = [&]() -> std::string { if (i + 1 >= argc) throw std::runtime_error("missing value for " + a); return argv[++i]; };
+            if (a == "-h" || a == "--help") { usage(); return 0; }
+            else if (a == "-x" || a == "--width") width = std::stoi(next());
+            else if (a == "-y" || a == "--height") height = std::stoi(next());
+            else if (a == "-s" || a == "--samples") spp = std::stoi(next());
+            else if (a == "-b" || a == "--batch") {} // always batch: there is no window
+            else if (a == "--settings") settings.load(next());
+            else if (a == "--env") env = next();
+            else if (a == "--bounces") bounces = std::stoi(next());
+            else if (a == "--iterations") iterations = (uint32_t)std::stoul(next());
+            else if (a == "--device") device = std::stoi(next());
+            else if (a == "--out") out = next();
+            else if (a == "--save-scene") saveScene = next();
+            else if (!a.empty() && a[0] == '-') throw std::runtime_error("unknown option " + a);
+            else scenes.push_back(a);
+        }
+        if (scenes.empty()) throw std::runtime_error("no scene given");
+        if (width < 0) width = settings.windowWidth;
+        if (height < 0) height = settings.windowHeight;
+        if (width <= 0 || height <= 0 || spp < 0) throw std::runtime_error("invalid width / height / samples");
+        if (bounces >= 0) settings.maxPathDepth = bounces;
+        if (env.empty()) env = settings.envMapName;
+    }
+    catch (const std::exception &e)
+    {
+        std::cerr << "fluctus_headless: " << e.what() << "\n";
+        usage();
+        return 2;
+    }
+
+    int rc = 0;
+    for (size_t si = 0; si < scenes.size(); si++)
+    {
+        try
+        {
+            flx::HostScene scene;
+            if (endsWith(scenes[si], ".flxs")) scene = flx::loadScene(scenes[si]);
+            else
+            {
+#ifdef FLX_WITH_REFERENCE_HOST
+                scene = flx::loadSceneWithReference(scenes[si], env);
+#else
+                throw std::runtime_error("this build reads .flxs scenes only (built without the reference tree); got " + scenes[si]);
+#endif
+            }
+            if (!saveScene.empty()) flx::saveScene(saveScene, scene);
+
+            // Tracer::renderSingle disables Russian roulette for fixed-spp renders (src/tracer.cpp:117-121)
+            flx::HeadlessTracer tracer(width, height, settings, device);
+            tracer.init(scene);
+            const auto t0 = std::chrono::steady_clock::now();
+            const flx::CudaContext::Totals t = tracer.render((uint32_t)spp, iterations ? iterations : (1u << 20));
+            const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            std::string file = out;
+            if (scenes.size() > 1) file = out.substr(0, out.rfind('.')) + "_" + std::to_string(si) + out.substr(out.rfind('.'));
+            tracer.saveImage(file);
+            printf("{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"triangles\": %zu, \"iterations\": %llu, \"primary\": %llu, "
+                   "\"extension\": %llu, \"shadow\": %llu, \"samples\": %llu, \"seconds\": %.4f, \"msamples_per_s\": %.3f, "
+                   "\"mrays_per_s\": %.3f, \"kernel_launches\": %llu, \"image\": \"%s\"}\n",
+                   scenes[si].c_str(), width, height, scene.tris.size(), (unsigned long long)t.iterations, (unsigned long long)t.primary,
+                   (unsigned long long)t.extension, (unsigned long long)t.shadow, (unsigned long long)t.samples, sec, t.samples / sec * 1e-6,
+                   (t.primary + t.extension + t.shadow) / sec * 1e-6, (unsigned long long)tracer.getClContext().launchCount(), file.c_str());
+        }
+        catch (const std::exception &e)
+        {
+            // the reference's loaders call exit(EXIT_FAILURE) (src/utils.h:28-34); CLContext errors throw runtime_error
+            std::cerr << "fluctus_headless: " << scenes[si] << ": " << e.what() << "\n";
+            rc = 1;
+        }
+    }
+    return rc;
+}

@@ -1,0 +1,270 @@
+// HeadlessTracer — the reference's render driver (`class Tracer`, reference src/tracer.{hpp,cpp}) without the
+// GLFW window: same settings surface (settings.json keys of src/settings.cpp:89-128 with the defaults of
+// :17-59), same parameter initialisation (resetParams :43-65, initCamera / initPostProcessing / initAreaLight
+// :1127-1168), same stage sequence (update :250-294 + :333-368; benchmark loop :633-645, :725-778), same image
+// export arithmetic (CLContext::saveImage, src/clcontext.cpp:404-483).  The device side is CudaContext.
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include "cuda_context.hpp"
+#include "host_scene.hpp"
+
+namespace flx {
+
+// ---- Settings: the reference's settings.json surface -----------------------------------------------------
+struct Settings
+{
+    std::string envMapName;
+    float renderScale = 1.0f;
+    int windowWidth = 640, windowHeight = 480;
+    uint32_t wfBufferSize = 1u << 20;
+    bool useRussianRoulette = false, useSeparateQueues = false;
+    int maxPathDepth = 10;
+    uint32_t maxSpp = 0, maxRenderTime = 0;
+    bool sampleImplicit = true, sampleExplicit = true, useEnvMap = false, useAreaLight = true;
+    int tonemap = 2;
+
+    // Reads the "release" object of a settings.json (reference src/settings.cpp:61-87).  A deliberately small
+    // scanner: `"key": value` pairs with number / bool / string values, nested objects ignored.
+    void load(const std::string &path, const std::string &section = "release")
+    {
+        std::ifstream in(path);
+        if (!in) throw std::runtime_error("cannot open settings file " + path);
+        std::stringstream ss; ss << in.rdbuf();
+        const std::string all = ss.str();
+        size_t a = all.find("\"" + section + "\"");
+        if (a == std::string::npos) return;
+        a = all.find('{', a);
+        int depth = 0; size_t b = a;
+        for (; b < all.size(); b++) { if (all[b] == '{') depth++; else if (all[b] == '}' && --depth == 0) break; }
+        const std::string obj = all.substr(a, b - a);
+        std::string s;
+        if (find(obj, "envMap", s)) envMapName = s;
+        if (find(obj, "renderScale", s)) renderScale = std::stof(s);
+        if (find(obj, "windowWidth", s)) windowWidth = std::stoi(s);
+        if (find(obj, "windowHeight", s)) windowHeight = std::stoi(s);
+        if (find(obj, "wfBufferSize", s)) wfBufferSize = (uint32_t)std::stoul(s);
+        if (find(obj, "useRussianRoulette", s)) useRussianRoulette = s == "true";
+        if (find(obj, "useSeparateQueues", s)) useSeparateQueues = s == "true";
+        if (find(obj, "maxPathDepth", s)) maxPathDepth = std::stoi(s);
+        if (find(obj, "maxSpp", s)) maxSpp = (uint32_t)std::stoul(s);
+        if (find(obj, "maxRenderTime", s)) maxRenderTime = (uint32_t)std::stoul(s);
+        if (find(obj, "sampleImplicit", s)) sampleImplicit = s == "true";
+        if (find(obj, "sampleExplicit", s)) sampleExplicit = s == "true";
+        if (find(obj, "useEnvMap", s)) useEnvMap = s == "true";
+        if (find(obj, "useAreaLight", s)) useAreaLight = s == "true";
+        if (find(obj, "tonemap", s)) tonemap = std::stoi(s);
+    }
+
+private:
+    static bool find(const std::string &obj, const std::string &key, std::string &out)
+    {
+        const size_t k = obj.find("\"" + key + "\"");
+        if (k == std::string::npos) return false;
+        size_t p = obj.find(':', k);
+        if (p == std::string::npos) return false;
+        p++;
+        while (p < obj.size() && isspace((unsigned char)obj[p])) p++;
+        if (p >= obj.size()) return false;
+        if (obj[p] == '"') { const size_t e = obj.find('"', p + 1); out = obj.substr(p + 1, e - p - 1); return true; }
+        size_t e = p;
+        while (e < obj.size() && obj[e] != ',' && obj[e] != '}' && !isspace((unsigned char)obj[e])) e++;
+        out = obj.substr(p, e - p);
+        return !out.empty();
+    }
+};
+
+inline flx_float3 f3(float x, float y, float z, float w = 0.0f) { flx_float3 v = {x, y, z, w}; return v; }
+
+class HeadlessTracer
+{
+public:
+    RenderParams params{};
+    Settings settings;
+    uint32_t iteration = 0;
+
+    HeadlessTracer(int width, int height, const Settings &s = Settings(), int device = 0, int rank = 0, int worldSize = 1)
+        : settings(s), clctx(s.wfBufferSize, device), rank(rank), worldSize(worldSize)
+    {
+        resetParams(width, height);
+        initCamera();
+        initPostProcessing();
+        initAreaLight();
+    }
+
+    CudaContext &getClContext() { return clctx; }
+
+    // Tracer::resetParams (src/tracer.cpp:43-65)
+    void resetParams(int width, int height)
+    {
+        params.width = (uint32_t)(width * settings.renderScale);
+        params.height = (uint32_t)(height * settings.renderScale);
+        params.useEnvMap = settings.useEnvMap; params.useAreaLight = settings.useAreaLight;
+        params.envMapStrength = 1.0f;
+        params.maxBounces = (uint32_t)settings.maxPathDepth;
+        params.sampleImpl = settings.sampleImplicit; params.sampleExpl = settings.sampleExplicit;
+        params.useRoulette = settings.useRussianRoulette; params.wfSeparateQueues = settings.useSeparateQueues;
+        params.maxSpp = settings.maxSpp;
+        params.width1 = 1.0f / (float)params.width; params.height1 = 1.0f / (float)params.height;
+    }
+    // Tracer::initCamera / initPostProcessing / initAreaLight (src/tracer.cpp:1127-1168), defaults src/settings.cpp:40-58
+    void initCamera()
+    {
+        flx_camera &c = params.camera;
+        c.pos = f3(0.0f, 1.0f, 3.5f); c.right = f3(1.0f, 0.0f, 0.0f); c.up = f3(0.0f, 1.0f, 0.0f); c.dir = f3(0.0f, 0.0f, -1.0f);
+        c.fov = 60.0f; c.fovSCALE = std::tan(0.5f * c.fov * 0.01745329251994329576923690768489f);
+        c.apertureSize = 0.0f; c.focalDist = 0.5f;
+    }
+    void setCamera(const float pos[3], const float dir[3], const float up[3], const float right[3], float fov)
+    {
+        flx_camera &c = params.camera;
+        c.pos = f3(pos[0], pos[1], pos[2]); c.dir = f3(dir[0], dir[1], dir[2]); c.up = f3(up[0], up[1], up[2]); c.right = f3(right[0], right[1], right[2]);
+        c.fov = fov; c.fovSCALE = std::tan(0.5f * fov * 0.01745329251994329576923690768489f);
+    }
+    void initPostProcessing() { params.ppParams.exposure = 1.0f; params.ppParams.tmOperator = (uint32_t)settings.tonemap; }
+    void initAreaLight()
+    {
+        flx_area_light &l = params.areaLight;
+        l.right = f3(0.0f, 0.0f, -1.0f); l.up = f3(0.0f, 1.0f, 0.0f); l.N = f3(-1.0f, 0.0f, 0.0f); l.pos = f3(1.0f, 1.0f, 0.0f, 1.0f);
+        l.E = f3(100.0f, 100.0f, 100.0f); l.size.x = 0.5f; l.size.y = 0.5f;
+    }
+
+    // Tracer::init (src/tracer.cpp:68-93): scene -> env map -> hierarchy -> worldRadius -> upload
+    void init(const HostScene &s)
+    {
+        if (s.hasEnvMap())
+        {
+            clctx.createEnvMap(s.envRgb.data(), s.envW, s.envH, s.envProb.data(), s.envAlias.data(), s.envPdf.data());
+            params.useEnvMap = 1; // Tracer::initEnvMap (src/tracer.cpp:922-931)
+        }
+        else params.useEnvMap = 0;
+        params.n_tris = (uint32_t)s.tris.size();
+        params.worldRadius = s.worldRadius();
+        clctx.uploadSceneData(s.tris.data(), s.tris.size(), s.indices.data(), s.indices.size(), s.nodes.data(), s.nodes.size(),
+                              s.materials.data(), s.materials.size(), s.textures.empty() ? nullptr : s.textures.data(), s.textures.size(),
+                              s.texels.empty() ? nullptr : s.texels.data(), s.texels.size());
+        clctx.setOptions(false, (uint32_t)rank * clctx.getNumTasks()); // sample sharding: seeds of one worldSize*N-task run
+        clctx.updateParams(params);
+        iteration = 0;
+    }
+
+    uint32_t cursorStart() const { return (uint32_t)(((uint64_t)rank * params.width * params.height) / (uint64_t)worldSize); }
+
+    // Tracer::update, wavefront branch (src/tracer.cpp:250-294, :333-336, :361-368): one interactive iteration
+    QueueCounters update()
+    {
+        const uint32_t maxBounces = params.maxBounces;
+        int N = 1;
+        if (iteration == 0)
+        {
+            params.maxBounces = std::min(2u, maxBounces); // 2-bounce preview
+            clctx.updateParams(params);
+            N = 3;
+            clctx.setPixelIndex(cursorStart());
+            clctx.enqueueWfResetKernel(params);
+            clctx.enqueueWfRaygenKernel(params);
+            clctx.enqueueWfExtRayKernel(params);
+            clctx.enqueueClearWfQueues();
+        }
+        QueueCounters cnt{};
+        for (int i = 0; i < N; i++)
+        {
+            clctx.enqueueWfLogicKernel(params, iteration == 0);
+            clctx.enqueueWfRaygenKernel(params);
+            clctx.enqueueWfMaterialKernels(params);
+            clctx.enqueueGetCounters(&cnt);
+            clctx.enqueueWfExtRayKernel(params);
+            clctx.enqueueWfShadowRayKernel(params);
+            clctx.enqueueClearWfQueues();
+        }
+        if (iteration == 0) { params.maxBounces = maxBounces; clctx.updateParams(params); }
+        clctx.enqueuePostprocessKernel(params);
+        clctx.finishQueue();
+        clctx.updatePixelIndex(params.width * params.height, cnt.raygenQueue);
+        clctx.statsAsync.extensionRays += cnt.extensionQueue;
+        clctx.statsAsync.shadowRays += cnt.shadowQueue;
+        clctx.statsAsync.primaryRays += cnt.raygenQueue;
+        clctx.statsAsync.samples += (iteration > 0) ? cnt.raygenQueue : 0;
+        iteration++;
+        return cnt;
+    }
+
+    // Fixed-budget render: Tracer::runBenchmarkFromFile's loop (src/tracer.cpp:633-645, :725-778) with the per-
+    // iteration host work moved to the device.  Stops after `spp` samples per pixel on this rank (counted like the
+    // reference: splattedSamples when maxSpp > 0, else regenerated paths) or after maxIterations passes.
+    CudaContext::Totals render(uint32_t spp, uint32_t maxIterations = 1u << 20, uint32_t batch = 16)
+    {
+        clctx.updateParams(params);
+        clctx.setPixelIndex(0);
+        clctx.render(0, true);
+        clctx.setPixelIndex(cursorStart());
+        const uint64_t target = (uint64_t)spp * params.width * params.height;
+        CudaContext::Totals t{};
+        for (uint32_t done = 0; done < maxIterations; done += batch)
+        {
+            clctx.render(std::min(batch, maxIterations - done));
+            t = clctx.getRenderTotals();
+            if (spp && (params.maxSpp > 0 ? t.splatted : t.samples) >= target) break;
+        }
+        clctx.enqueuePostprocessKernel(params);
+        clctx.finishQueue();
+        return t;
+    }
+
+    // CLContext::saveImage (src/clcontext.cpp:404-483).  ".ppm": tonemapped preview, clamp, (uchar)(255*x), flipped
+    // vertically (the reference's image origin is bottom-left).  ".pfm": raw accumulation / sample count (the
+    // reference's ".hdr" branch), float RGB, bottom-up as PFM defines it.
+    void saveImage(const std::string &filename)
+    {
+        const uint32_t w = params.width, h = params.height;
+        const bool pfm = filename.size() > 4 && filename.substr(filename.size() - 4) == ".pfm";
+        FILE *f = fopen(filename.c_str(), "wb");
+        if (!f) throw std::runtime_error("cannot write " + filename);
+        if (pfm)
+        {
+            const std::vector<float> px = clctx.readPixels(FLX_BUF_PIXELS);
+            fprintf(f, "PF\n%u %u\n-1.0\n", w, h);
+            std::vector<float> row(3 * (size_t)w);
+            for (uint32_t y = 0; y < h; y++)
+            {
+                for (uint32_t x = 0; x < w; x++)
+                {
+                    const float *p = &px[4 * ((size_t)y * w + x)];
+                    const float a = p[3] > 0.0f ? p[3] : 1.0f;
+                    row[3 * x] = p[0] / a; row[3 * x + 1] = p[1] / a; row[3 * x + 2] = p[2] / a;
+                }
+                fwrite(row.data(), 4, row.size(), f);
+            }
+        }
+        else
+        {
+            clctx.enqueuePostprocessKernel(params);
+            const std::vector<float> px = clctx.readPixels(FLX_BUF_PREVIEW);
+            fprintf(f, "P6\n%u %u\n255\n", w, h);
+            std::vector<unsigned char> row(3 * (size_t)w);
+            for (uint32_t y = 0; y < h; y++)
+            {
+                const uint32_t sy = h - 1 - y;
+                for (uint32_t x = 0; x < w; x++)
+                    for (int c = 0; c < 3; c++)
+                    {
+                        float v = px[4 * ((size_t)sy * w + x) + c];
+                        v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+                        row[3 * x + c] = (unsigned char)(255.0f * v);
+                    }
+                fwrite(row.data(), 1, row.size(), f);
+            }
+        }
+        fclose(f);
+    }
+
+private:
+    CudaContext clctx; // name kept from the reference (src/tracer.hpp:131)
+    int rank, worldSize;
+};
+
+} // namespace flx

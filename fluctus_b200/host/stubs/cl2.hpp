@@ -1,5 +1,5 @@
 // Typedef-only stand-in for the OpenCL C++ header, so that the reference's HOST sources
-// (scene/bvh/sbvh/envmap/settings) compile headless. Test infrastructure only (oracle/).
+// (scene/bvh/sbvh/envmap/settings) compile headless. Used by the headless host build (fluctus_b200/host) and by oracle/ref_host.
 #pragma once
 #include <cstdint>
 #include <cstddef>

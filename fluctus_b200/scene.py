@@ -149,3 +149,44 @@ def bench_rays(n, bounds, first=0):
     rays[:, 3] = np.float32(3.402823466e+38)
     rays[:, 4], rays[:, 5], rays[:, 6] = s * np.cos(phi).astype(np.float32), s * np.sin(phi).astype(np.float32), z
     return rays
+
+
+# ---- .flxs: the flat container the C++ host reads (fluctus_b200/host/host_scene.hpp) ------------------------
+FLXS_MAGIC = b"FLXS0001"
+
+
+def save_flxs(path, scene, env=None):
+    tex = np.ascontiguousarray(scene.get("textures", np.zeros(0, TEX_DT)))
+    texels = np.ascontiguousarray(scene.get("texels", np.zeros(0, np.uint8)), np.uint8)
+    eh, ew = (env["rgb"].shape[:2] if env is not None else (0, 0))
+    hdr = np.array([len(scene["tris"]), len(scene["indices"]), len(scene["nodes"]), len(scene["materials"]), len(tex),
+                    texels.size, ew, eh], np.uint64)
+    with open(path, "wb") as f:
+        f.write(FLXS_MAGIC)
+        f.write(hdr.tobytes())
+        for a in (scene["tris"], np.asarray(scene["indices"], np.uint32), scene["nodes"], scene["materials"], tex, texels):
+            f.write(np.ascontiguousarray(a).tobytes())
+        if env is not None:
+            f.write(np.ascontiguousarray(env["rgb"], np.float32).tobytes())
+            f.write(np.ascontiguousarray(env["prob"], np.float32).tobytes())
+            f.write(np.ascontiguousarray(env["alias"], np.int32).tobytes())
+            f.write(np.ascontiguousarray(env["pdf"], np.float32).tobytes())
+
+
+def load_flxs(path):
+    """Returns (scene dict, env dict or None)."""
+    with open(path, "rb") as f:
+        if f.read(8) != FLXS_MAGIC:
+            raise ValueError("not a .flxs file: %s" % path)
+        nt, ni, nn, nm, ntex, nb, ew, eh = (int(x) for x in np.frombuffer(f.read(64), np.uint64))
+
+        def rd(dtype, n):
+            return np.frombuffer(f.read(np.dtype(dtype).itemsize * n), dtype).copy()
+        scene = dict(tris=rd(TRI_DT, nt), indices=rd(np.uint32, ni), nodes=rd(NODE_DT, nn), materials=rd(MAT_DT, nm),
+                     textures=rd(TEX_DT, ntex), texels=rd(np.uint8, nb))
+        scene["bounds"] = scene_bounds(scene)
+        env = None
+        if ew * eh:
+            n = ew * eh
+            env = dict(rgb=rd(np.float32, 3 * n).reshape(eh, ew, 3), prob=rd(np.float32, n), alias=rd(np.int32, n), pdf=rd(np.float32, n))
+    return scene, env

@@ -2,58 +2,11 @@
 // (src/scene.cpp, bvh.cpp, sbvh.cpp, envmap.cpp ... compiled in place from $FLUCTUS_REF by
 // oracle/ref_host/Makefile into oracle/_ref/libflxref_host.so).  It lets tests and the scene
 // cache tool obtain exactly the byte layouts CLContext::uploadSceneData / createEnvMap hand to
-// the device (reference src/clcontext.cpp:485-529, 540-629).  Nothing in the product links it.
-#include "scene.hpp"
-#include "progressview.hpp"
-#include "sbvh.hpp"
-#include "envmap.hpp"
-#include "texture.hpp"
+// the device (reference src/clcontext.cpp:485-529, 540-629).  Nothing in the product links this file; the
+// headless host (fluctus_b200/host) has its own loader on the same glue (ref_glue.hpp).
+#include "ref_glue.hpp" // fluctus_b200/host: headless replacements for progressview.cpp / texture.cpp + BVH accessor
 #include <cstdio>
 #include <memory>
-
-#define STB_IMAGE_IMPLEMENTATION
-#define STBI_ONLY_JPEG
-#define STBI_ONLY_PNG
-#define STBI_ONLY_BMP
-#define STBI_ONLY_TGA
-#include "stb_image.h" // found on the include path inside the reference tree (nanovg copy)
-
-// ---- replacements for the two reference TUs that need GUI / DevIL ---------------------------
-ProgressView::ProgressView(nanogui::Screen *) {}
-void ProgressView::showError(const std::string &) {}
-void ProgressView::showMessage(const std::string &, float) {}
-void ProgressView::showMessage(const std::string &, const std::string &) {}
-void ProgressView::showMessage(const std::string &, const std::string &, float) {}
-void ProgressView::center() {}
-void ProgressView::hide() {}
-
-// Same contract as reference src/texture.cpp:16-41 (RGBA8, top-left origin like DevIL's default)
-Texture::Texture(const std::string path, const std::string filename)
-{
-    int w = 0, h = 0, n = 0;
-    unsigned char *px = stbi_load(path.c_str(), &w, &h, &n, 4);
-    if (px)
-    {
-        width = (cl_uint)w; height = (cl_uint)h;
-        data = new cl_uchar[(size_t)w * h * 4];
-        memcpy(data, px, (size_t)w * h * 4);
-        stbi_image_free(px);
-        name = filename;
-    }
-    else
-    {
-        width = height = 0; data = nullptr; name = "error";
-    }
-}
-
-// BVH keeps its arrays protected but befriends CLContext (reference src/bvh.hpp:13).  This TU
-// never sees the real class, so it supplies a local one with the accessor we need.
-class CLContext
-{
-public:
-    static std::vector<Node> &nodes(BVH *b) { return b->m_nodes; }
-    static std::vector<U32> &indices(BVH *b) { return b->m_indices; }
-};
 
 struct RefScene
 {
