@@ -102,7 +102,7 @@ def test_product_does_not_touch_the_oracle():
             for f in files:
                 if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp", "Makefile")):
                     text = open(os.path.join(dirpath, f), errors="ignore").read()
-                    if re.search(r"(from|import)\s+oracle|liboracle|oracle/", text):
+                    if re.search(r"(from|import)\s+oracle|liboracle|libflxref|pyoracle|#include\s+\"[^\"]*oracle|-[LI]\S*oracle", text):
                         bad.append(os.path.join(dirpath, f))
     assert not bad, bad
     import fluctus_b200 as fx
