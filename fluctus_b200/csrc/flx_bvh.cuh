@@ -75,61 +75,150 @@ struct RayHit
 // triangle tests.  Only the COUNT=true instantiations touch them; the timed kernels do not.
 struct TravCount { unsigned int inner, leaf, tri; };
 
-// Closest hit (ANY=false): src/bvh.cl:234-310.  Any hit (ANY=true): src/bvh.cl:312-373, returns
-// with slot >= 0 as soon as a triangle with 0 < t < tmax is found.
-template <bool ANY, bool COUNT = false>
-FLX_DEV RayHit traverse(const DevBVH &bvh, f3 o, f3 d, float tmax, TravCount *cnt = nullptr)
+// ---------------------------------------------------------------------------------------------------
+// Traversal engine: persistent warps, ray replacement, phase voting.
+//
+// Closest hit (ANY=false) follows src/bvh.cl:234-310, any hit (ANY=true) src/bvh.cl:312-373 (returns as
+// soon as a triangle with 0 < t < tmax is found).  The PER-RAY sequence of box tests, pushes, pops and
+// triangle tests is exactly the reference's; what is new is how the work of 32 rays is issued by a warp.
+// A lane that owns a ray is in one of three states: INNER (next op: test the two child boxes of node
+// `cur`), LEAF (next op: one triangle test at leaf slot ~cur) or DONE (result ready to be written).  In the
+// reference — and in a straightforward CUDA port — every loop iteration executes the inner-node body AND
+// the leaf body under partial masks, and the warp idles until its slowest ray is finished; ncu showed 10 of
+// 32 lanes active per instruction for that design (profiles/r1a_k_ext_full.md).  Here each iteration the warp
+// VOTES (ballot + popc) and executes exactly ONE body for the lanes that need it:
+//   * retire + refill when >= FLX_VOTE_RETIRE lanes are DONE or idle (or nothing else can run): DONE lanes
+//     write their results together and idle lanes take the next rays with ONE atomicAdd per warp;
+//   * else the triangle body when >= FLX_VOTE_LEAF lanes wait on a leaf (or no lane is INNER);
+//   * else the inner-node body.
+// Once a body is chosen the warp stays in it while >= FLX_STAY_* lanes still have work of that kind (one ballot
+// per pass instead of the full vote).  Lanes whose state was not chosen wait; they are picked up as soon as
+// enough peers join them.  Thresholds were tuned on B200 with tools/tune_vote.sh (kitchen render + cfg5 rays).
+// A Job supplies the rays and consumes the results:
+//     bool load(unsigned k, f3 &o, f3 &d, float &tmax)   // false: ray k needs no traversal (already resolved)
+//     void store(const RayHit &h, f3 o, f3 d)            // result of the ray loaded last by this lane
+#ifndef FLX_VOTE_RETIRE
+#define FLX_VOTE_RETIRE 8
+#endif
+#ifndef FLX_VOTE_LEAF
+#define FLX_VOTE_LEAF 8
+#endif
+#ifndef FLX_STAY_LEAF
+#define FLX_STAY_LEAF 4
+#endif
+#ifndef FLX_STAY_INNER
+#define FLX_STAY_INNER 8
+#endif
+#define FLX_TRAV_DONE ((int)0x80000000) // not a valid ref: leaf refs are ~slot with slot < 0x7fffffff
+
+template <bool ANY, bool COUNT, class Job>
+FLX_DEV void traceLoop(const DevBVH &bvh, Job &job, unsigned int *cursor, unsigned int total, TravCount &cnt)
 {
-    RayHit best; best.t = tmax; best.u = 0.0f; best.v = 0.0f; best.slot = -1;
-    const f3 dinv = mk3(recip(d.x), recip(d.y), recip(d.z));
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
     int stack[FLX_STACK_SIZE];
-    int sp = 0;
-    int cur = bvh.rootRef;
+    int sp = 0, cur = FLX_TRAV_DONE;
+    bool active = false, poolEmpty = false;
+    f3 o = mk3(0.0f), d = mk3(0.0f), dinv = mk3(0.0f);
+    RayHit best; best.t = 0.0f; best.u = 0.0f; best.v = 0.0f; best.slot = -1;
+
     while (true)
     {
-        if (cur >= 0)
+        const bool isDone = active && cur == FLX_TRAV_DONE;
+        const unsigned mInner = __ballot_sync(FULL, active && cur >= 0);
+        const unsigned mLeaf = __ballot_sync(FULL, active && cur < 0 && cur != FLX_TRAV_DONE);
+        const unsigned mDone = __ballot_sync(FULL, isDone);
+        const unsigned mIdle = poolEmpty ? 0u : __ballot_sync(FULL, !active);
+        const unsigned runnable = mInner | mLeaf;
+        const int waiting = __popc(mDone | mIdle);
+
+        if (waiting >= FLX_VOTE_RETIRE || (runnable == 0u && waiting > 0))
         {
-            if (COUNT) cnt->inner++;
-            const float4 *n = bvh.nodes + 4 * (size_t)cur;
-            const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
-            float lnear, rnear;
-            const bool lh = slabTest(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, dinv, best.t, lnear);
-            const bool rh = slabTest(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, dinv, best.t, rnear);
-            const int l = __float_as_int(n3.x), r = __float_as_int(n3.y);
-            if (lh && rh)
+            // ---- retire finished rays, hand the next rays of the pool to the free lanes ----------------
+            if (isDone) { job.store(best, o, d); active = false; }
+            if (!poolEmpty)
             {
-                int nearRef = l, farRef = r;
-                if (rnear < lnear) { nearRef = r; farRef = l; }
-                stack[sp++] = farRef;
-                cur = nearRef;
-                continue;
+                const unsigned freeMask = mDone | mIdle;
+                const unsigned n = (unsigned)__popc(freeMask);
+                unsigned base = 0u;
+                if (lane == 0u) base = atomicAdd(cursor, n);
+                base = __shfl_sync(FULL, base, 0);
+                if (!active)
+                {
+                    const unsigned k = base + (unsigned)__popc(freeMask & ltMask);
+                    if (k < total)
+                    {
+                        float tmax;
+                        if (job.load(k, o, d, tmax))
+                        {
+                            dinv = mk3(recip(d.x), recip(d.y), recip(d.z));
+                            best.t = tmax; best.u = 0.0f; best.v = 0.0f; best.slot = -1;
+                            cur = bvh.rootRef; sp = 0; active = true;
+                        }
+                    }
+                }
+                if (base + n >= total) poolEmpty = true;
             }
-            if (lh) { cur = l; continue; }
-            if (rh) { cur = r; continue; }
+        }
+        else if (runnable == 0u) break; // nothing running, nothing to retire, pool empty
+        else if (mLeaf != 0u && (__popc(mLeaf) >= FLX_VOTE_LEAF || mInner == 0u))
+        {
+            // ---- triangle tests, one per waiting lane and pass: leaf slots in index order, strictly-closer
+            // wins.  The warp stays in this body while enough lanes still hold leaf work (one ballot per pass
+            // instead of the full vote).
+            unsigned m;
+            do
+            {
+                if (active && cur < 0 && cur != FLX_TRAV_DONE)
+                {
+                    const int slot = ~cur;
+                    if (COUNT) cnt.tri++;
+                    const float4 *q = bvh.slots + 3 * (size_t)slot;
+                    const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2);
+                    float t, u, v;
+                    bool found = false;
+                    if (triTest(o, d, mk3(q0), mk3(q1), mk3(q2), t, u, v) && t > 0.0f && t < best.t)
+                    {
+                        best.t = t; best.u = u; best.v = v; best.slot = slot;
+                        found = true;
+                    }
+                    if (ANY && found) cur = FLX_TRAV_DONE;
+                    else if (__float_as_int(q1.w) != 0) cur = sp ? stack[--sp] : FLX_TRAV_DONE; // last slot of the leaf
+                    else cur = cur - 1;                                                         // ~(slot + 1)
+                }
+                m = __ballot_sync(FULL, active && cur < 0 && cur != FLX_TRAV_DONE);
+            } while (__popc(m) >= FLX_STAY_LEAF);
         }
         else
         {
-            int slot = ~cur;
-            if (COUNT) cnt->leaf++;
-            while (true)
+            // ---- inner-node steps: both child boxes, near child first --------------------------------------
+            unsigned m;
+            do
             {
-                if (COUNT) cnt->tri++;
-                const float4 *q = bvh.slots + 3 * (size_t)slot;
-                const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2);
-                float t, u, v;
-                if (triTest(o, d, mk3(q0), mk3(q1), mk3(q2), t, u, v) && t > 0.0f && t < best.t)
+                if (active && cur >= 0)
                 {
-                    best.t = t; best.u = u; best.v = v; best.slot = slot;
-                    if (ANY) return best;
+                    if (COUNT) cnt.inner++;
+                    const float4 *n = bvh.nodes + 4 * (size_t)cur;
+                    const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
+                    float lnear, rnear;
+                    const bool lh = slabTest(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, dinv, best.t, lnear);
+                    const bool rh = slabTest(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, dinv, best.t, rnear);
+                    const int l = __float_as_int(n3.x), r = __float_as_int(n3.y);
+                    if (lh && rh)
+                    {
+                        const bool swap = rnear < lnear; // left first on equal entry distance (src/bvh.cl:293-300)
+                        stack[sp++] = swap ? l : r;
+                        cur = swap ? r : l;
+                    }
+                    else if (lh) cur = l;
+                    else if (rh) cur = r;
+                    else cur = sp ? stack[--sp] : FLX_TRAV_DONE;
+                    if (COUNT && cur < 0 && cur != FLX_TRAV_DONE) cnt.leaf++;
                 }
-                if (__float_as_int(q1.w) != 0) break;
-                slot++;
-            }
+                m = __ballot_sync(FULL, active && cur >= 0);
+            } while (__popc(m) >= FLX_STAY_INNER);
         }
-        if (sp == 0) break;
-        cur = stack[--sp];
     }
-    return best;
 }
 
 FLX_DEV f3 lerp3(float u, float v, f3 a, f3 b, f3 c) // src/utils.cl:25-28

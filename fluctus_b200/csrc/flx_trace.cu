@@ -1,22 +1,13 @@
 // Ray-traversal kernels (closest hit / any hit), both as wavefront stages (reference
 // src/wf_extrays.cl, src/wf_shadowrays.cl) and as plain ray-batch entry points.
 //
-// Persistent warps: the grid is a fixed multiple of the SM count and every warp pulls the next 32
-// queue entries with one atomic (lane 0) + shuffle broadcast until the work is gone.
+// Persistent warps: the grid is a fixed multiple of the SM count; lanes that run out of work pull the
+// next queue entries with one atomic per warp (see traceLoop in flx_bvh.cuh) until the work is gone.
 // COUNT=true instantiations additionally accumulate visit counters (inner pops, leaf visits,
 // triangle tests, hits, rays) for the algorithmic-bytes figure; they are never the timed ones.
 #include "flx_internal.h"
 
 #define FLX_TRACE_THREADS 128
-
-FLX_DEV bool fetchWork(unsigned int *cursor, unsigned int total, unsigned int &idx)
-{
-    unsigned int base = 0;
-    if ((threadIdx.x & 31) == 0) base = atomicAdd(cursor, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    idx = base + (threadIdx.x & 31);
-    return base < total;
-}
 
 FLX_DEV void flushCounts(unsigned long long *stats, const TravCount &c, unsigned int hits, unsigned int rays)
 {
@@ -43,25 +34,21 @@ FLX_DEV AreaLightGeom makeLightGeom(const flx_area_light &al)
     return g;
 }
 
-// wf_extrays.cl:5-36
-template <bool COUNT>
-__global__ void __launch_bounds__(FLX_TRACE_THREADS)
-k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
-      unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
-{
-    const unsigned int total = counters->extensionQueue;
-    const bool lightOn = params.sampleImpl && params.useAreaLight;
-    TravCount cnt = {0u, 0u, 0u};
-    unsigned int nHits = 0, nRays = 0;
-    unsigned int k;
-    while (fetchWork(cursor, total, k))
-    {
-        if (k >= total) continue;
-        const uint32_t gid = queue[k];
-        const float4 r0 = st.ray0[gid], r1 = st.ray1[gid];
-        const f3 o = mk3(r0), d = mk3(r1);
-        const RayHit h = traverse<false, COUNT>(bvh, o, d, FLX_FLT_MAX, &cnt);
+// ---- jobs: where the rays of each kernel come from and where the results go ------------------------------
 
+// wf_extrays.cl:5-36
+struct ExtJob
+{
+    const DevBVH &bvh; const PathState &st; const uint32_t *queue; const flx_render_params &params;
+    uint32_t gid; unsigned int nHits, nRays;
+    FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
+    {
+        gid = queue[k];
+        o = mk3(st.ray0[gid]); d = mk3(st.ray1[gid]); tmax = FLX_FLT_MAX;
+        return true;
+    }
+    FLX_DEV void store(const RayHit &h, f3 o, f3 d)
+    {
         f3 P = mk3(0.0f), N = mk3(0.0f);
         float uvx = 0.0f, uvy = 0.0f, t = FLX_FLT_MAX;
         int hi = -1, matId = -1, al = 0;
@@ -70,8 +57,8 @@ k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_qu
             t = h.t;
             fetchHitAttribs(bvh, h, o, d, hi, matId, P, N, uvx, uvy);
         }
-        if (COUNT) { nRays++; nHits += (h.slot >= 0); }
-        if (lightOn)
+        nRays++; nHits += (h.slot >= 0);
+        if (params.sampleImpl && params.useAreaLight) // wf_extrays.cl:27-28
         {
             const AreaLightGeom g = makeLightGeom(params.areaLight);
             if (intersectLight(g, o, d, t)) { al = 1; P = o + t * d; N = g.N; hi = 0; matId = 0; }
@@ -79,60 +66,50 @@ k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_qu
         st.hit0[gid] = mk4(P, t);
         st.hit1[gid] = mk4i(N, hi);
         st.hit2[gid] = make_float4(uvx, uvy, __int_as_float(matId), __int_as_float(al));
-        st.ray1[gid].w = __uint_as_float(__float_as_uint(r1.w) + 1u); // pathLen += 1
+        uint32_t *len = reinterpret_cast<uint32_t *>(&st.ray1[gid].w);
+        *len = *len + 1u; // pathLen += 1
     }
-    if (COUNT) flushCounts(stats, cnt, nHits, nRays);
-}
+};
 
 // wf_shadowrays.cl:6-39
-template <bool COUNT>
-__global__ void __launch_bounds__(FLX_TRACE_THREADS)
-k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
-         unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
+struct ShadowJob
 {
-    const unsigned int total = counters->shadowQueue;
-    TravCount cnt = {0u, 0u, 0u};
-    unsigned int nHits = 0, nRays = 0;
-    unsigned int k;
-    while (fetchWork(cursor, total, k))
+    const PathState &st; const uint32_t *queue; const flx_render_params &params;
+    uint32_t gid; unsigned int nHits, nRays;
+    FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
     {
-        if (k >= total) continue;
-        const uint32_t gid = queue[k];
-        const float4 s0 = st.shw0[gid], s1 = st.shw1[gid];
-        const f3 o = mk3(s0), d = mk3(s1);
-        const float lenL = s0.w;
-        bool occluded = false;
-        if (params.useAreaLight)
+        gid = queue[k];
+        const float4 s0 = st.shw0[gid];
+        o = mk3(s0); d = mk3(st.shw1[gid]); tmax = s0.w;
+        if (params.useAreaLight) // the light quad occludes from its front side (wf_shadowrays.cl:31-33)
         {
-            float t = lenL;
-            occluded = intersectLight(makeLightGeom(params.areaLight), o, d, t);
+            float t = tmax;
+            if (intersectLight(makeLightGeom(params.areaLight), o, d, t)) { st.shadowBlocked[gid] = 1u; return false; }
         }
-        if (!occluded)
-        {
-            occluded = traverse<true, COUNT>(bvh, o, d, lenL, &cnt).slot >= 0;
-            if (COUNT) { nRays++; nHits += occluded; }
-        }
-        st.shadowBlocked[gid] = occluded ? 1u : 0u;
+        return true;
     }
-    if (COUNT) flushCounts(stats, cnt, nHits, nRays);
-}
-
-// ray-batch closest hit: rays as 2 x float4 {o.xyz, tmax} {d.xyz, -}
-template <bool COUNT>
-__global__ void __launch_bounds__(FLX_TRACE_THREADS)
-k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
-              int32_t *__restrict__ hitI, float *__restrict__ hitT, float4 *__restrict__ hits)
-{
-    TravCount cnt = {0u, 0u, 0u};
-    unsigned int nHits = 0, nRays = 0;
-    unsigned int k;
-    while (fetchWork(cursor, n, k))
+    FLX_DEV void store(const RayHit &h, f3, f3)
     {
-        if (k >= n) continue;
-        const float4 r0 = __ldg(rays + 2 * (size_t)k), r1 = __ldg(rays + 2 * (size_t)k + 1);
-        const f3 o = mk3(r0), d = mk3(r1);
-        const RayHit h = traverse<false, COUNT>(bvh, o, d, r0.w, &cnt);
-        if (COUNT) { nRays++; nHits += (h.slot >= 0); }
+        nRays++; nHits += (h.slot >= 0);
+        st.shadowBlocked[gid] = h.slot >= 0 ? 1u : 0u;
+    }
+};
+
+// ray batch, closest hit: rays as 2 x float4 {o.xyz, tmax} {d.xyz, -}
+struct BatchJob
+{
+    const DevBVH &bvh; const float4 *rays; int32_t *hitI; float *hitT; float4 *hits;
+    unsigned int k; unsigned int nHits, nRays;
+    FLX_DEV bool load(unsigned int kk, f3 &o, f3 &d, float &tmax)
+    {
+        k = kk;
+        const float4 r0 = __ldg(rays + 2 * (size_t)kk), r1 = __ldg(rays + 2 * (size_t)kk + 1);
+        o = mk3(r0); d = mk3(r1); tmax = r0.w;
+        return true;
+    }
+    FLX_DEV void store(const RayHit &h, f3 o, f3 d)
+    {
+        nRays++; nHits += (h.slot >= 0);
         int hi = -1, matId = -1;
         f3 P = mk3(0.0f), N = mk3(0.0f);
         float uvx = 0.0f, uvy = 0.0f;
@@ -152,7 +129,57 @@ k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsig
             o4[3] = make_float4(__int_as_float(0), __int_as_float(matId), 0.0f, 0.0f);
         }
     }
-    if (COUNT) flushCounts(stats, cnt, nHits, nRays);
+};
+
+struct AnyBatchJob
+{
+    const float4 *rays; uint8_t *occ;
+    unsigned int k; unsigned int nHits, nRays;
+    FLX_DEV bool load(unsigned int kk, f3 &o, f3 &d, float &tmax)
+    {
+        k = kk;
+        const float4 r0 = __ldg(rays + 2 * (size_t)kk), r1 = __ldg(rays + 2 * (size_t)kk + 1);
+        o = mk3(r0); d = mk3(r1); tmax = r0.w;
+        return true;
+    }
+    FLX_DEV void store(const RayHit &h, f3, f3)
+    {
+        nRays++; nHits += (h.slot >= 0);
+        occ[k] = h.slot >= 0 ? 1 : 0;
+    }
+};
+
+template <bool COUNT>
+__global__ void __launch_bounds__(FLX_TRACE_THREADS)
+k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
+      unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
+{
+    ExtJob job = {bvh, st, queue, params, 0u, 0u, 0u};
+    TravCount cnt = {0u, 0u, 0u};
+    traceLoop<false, COUNT>(bvh, job, cursor, counters->extensionQueue, cnt);
+    if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(FLX_TRACE_THREADS)
+k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
+         unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
+{
+    ShadowJob job = {st, queue, params, 0u, 0u, 0u};
+    TravCount cnt = {0u, 0u, 0u};
+    traceLoop<true, COUNT>(bvh, job, cursor, counters->shadowQueue, cnt);
+    if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(FLX_TRACE_THREADS)
+k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
+              int32_t *__restrict__ hitI, float *__restrict__ hitT, float4 *__restrict__ hits)
+{
+    BatchJob job = {bvh, rays, hitI, hitT, hits, 0u, 0u, 0u};
+    TravCount cnt = {0u, 0u, 0u};
+    traceLoop<false, COUNT>(bvh, job, cursor, n, cnt);
+    if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
 template <bool COUNT>
@@ -160,18 +187,10 @@ __global__ void __launch_bounds__(FLX_TRACE_THREADS)
 k_any_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
             uint8_t *__restrict__ occ)
 {
+    AnyBatchJob job = {rays, occ, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    unsigned int nHits = 0, nRays = 0;
-    unsigned int k;
-    while (fetchWork(cursor, n, k))
-    {
-        if (k >= n) continue;
-        const float4 r0 = __ldg(rays + 2 * (size_t)k), r1 = __ldg(rays + 2 * (size_t)k + 1);
-        const bool hit = traverse<true, COUNT>(bvh, mk3(r0), mk3(r1), r0.w, &cnt).slot >= 0;
-        if (COUNT) { nRays++; nHits += hit; }
-        occ[k] = hit ? 1 : 0;
-    }
-    if (COUNT) flushCounts(stats, cnt, nHits, nRays);
+    traceLoop<true, COUNT>(bvh, job, cursor, n, cnt);
+    if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
 // ---------------------------------------------------------------------------------------------
