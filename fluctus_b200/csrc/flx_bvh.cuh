@@ -8,8 +8,8 @@
 //       both children's boxes live in the parent, so one node visit is one 64-byte fetch instead
 //       of the reference's 48 B node + two 48 B child fetches (src/bvh.cl:250, :284-285).
 //       ref >= 0: index of an inner node in this array;  ref < 0: ~ref = first leaf slot.
-//   leaf slot   48 B = 3 x float4   {v0.xyz, triIndex} {v1.xyz, lastFlag} {v2.xyz, matId}
-//       triangle positions stored in index-list order (one slot per entry of the reference's
+//   leaf slot   48 B = 3 x float4   {v0.xyz, triIndex} {(v1-v0).xyz, lastFlag} {(v2-v0).xyz, matId}
+//       first vertex + the two edge vectors of Moeller-Trumbore, stored in index-list order (one slot per entry of the reference's
 //       `indices`), so the indices[i] -> tris[...] double indirection of src/bvh.cl:262 is gone;
 //       lastFlag != 0 marks the last slot of a leaf, which replaces nPrims.
 //   shading rec 64 B = 4 x float4   n0.xyz n1.xyz n2.xyz uv0 uv1 uv2 matId, indexed by triangle id,
@@ -45,11 +45,11 @@ FLX_DEV bool slabTest(float bx0, float by0, float bz0, float bx1, float by1, flo
     return tmin < tMaxPrev;
 }
 
-// src/intersect.cl:63-93 (Moeller-Trumbore, EPSILON 1e-12f)
-FLX_DEV bool triTest(f3 o, f3 d, f3 p0, f3 p1, f3 p2, float &t, float &u, float &v)
+// src/intersect.cl:63-93 (Moeller-Trumbore, EPSILON 1e-12f) with the two edge vectors s1 = v1 - v0 and
+// s2 = v2 - v0 supplied by the caller: the leaf slots store them precomputed (one IEEE subtraction per
+// component, done once at upload instead of once per test — same operands, same rounding, same bits).
+FLX_DEV bool triTestEdges(f3 o, f3 d, f3 p0, f3 s1, f3 s2, float &t, float &u, float &v)
 {
-    const f3 s1 = p1 - p0;
-    const f3 s2 = p2 - p0;
     const f3 pvec = cross(d, s2);
     const float det = dot(s1, pvec);
     if (fabsf(det) < 1e-12f) return false;
@@ -63,6 +63,10 @@ FLX_DEV bool triTest(f3 o, f3 d, f3 p0, f3 p1, f3 p2, float &t, float &u, float 
     t = dot(s2, qvec) * iDet;
     if (t < 0.0f) return false;
     return true;
+}
+FLX_DEV bool triTest(f3 o, f3 d, f3 p0, f3 p1, f3 p2, float &t, float &u, float &v)
+{
+    return triTestEdges(o, d, p0, p1 - p0, p2 - p0, t, u, v);
 }
 
 struct RayHit
@@ -177,7 +181,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, Job &job, unsigned int *cursor, unsign
                     const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2);
                     float t, u, v;
                     bool found = false;
-                    if (triTest(o, d, mk3(q0), mk3(q1), mk3(q2), t, u, v) && t > 0.0f && t < best.t)
+                    if (triTestEdges(o, d, mk3(q0), mk3(q1), mk3(q2), t, u, v) && t > 0.0f && t < best.t)
                     {
                         best.t = t; best.u = u; best.v = v; best.slot = slot;
                         found = true;

@@ -38,7 +38,7 @@ struct PathState
 
 struct Queues
 {
-    uint32_t *q[FLX_NUM_QUEUES]; // N entries each (reference src/clcontext.cpp:130-138)
+    uint32_t *q[FLX_NUM_QUEUES]; // N entries each (reference src/clcontext.cpp:130-138); one allocation: q[i] = q[0] + i * N
     flx_queue_counters *counters; // device copy of QueueCounters
 };
 

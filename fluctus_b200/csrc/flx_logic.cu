@@ -4,6 +4,12 @@
 #include "flx_bxdf.cuh"
 
 #define FLX_WF_THREADS 256
+#ifndef FLX_LOGIC_MIN_BLOCKS
+#define FLX_LOGIC_MIN_BLOCKS 1
+#endif
+#ifndef FLX_MAT_MIN_BLOCKS
+#define FLX_MAT_MIN_BLOCKS 1
+#endif
 
 FLX_DEV uint32_t warpPush(uint32_t *counter, bool pred) // see flx_wavefront.cu
 {
@@ -57,7 +63,7 @@ FLX_DEV int materialQueueOf(int type, bool separate)
 
 FLX_DEV uint32_t *counterOf(flx_queue_counters *c, int q) { return ((uint32_t *)c) + q; } // same order as FLX_Q_*
 
-__global__ void __launch_bounds__(FLX_WF_THREADS)
+__global__ void __launch_bounds__(FLX_WF_THREADS, FLX_LOGIC_MIN_BLOCKS)
 k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env, uint32_t N, uint32_t firstIteration,
         int denoiserAOV, const __grid_constant__ flx_render_params params)
 {
@@ -238,32 +244,36 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
         }
 
         // ---- warp-aggregated compaction into the raygen / shadow / material queues ----------------
+        // One ballot per queue, then lane q reserves the slots of queue q: the (up to nine) atomicAdds of a
+        // warp are issued by different lanes in ONE instruction, i.e. one round trip to L2 instead of one per
+        // queue (the per-queue version spent half of the kernel's stall samples waiting on them one after the
+        // other).  Counter q of QueueCounters belongs to queue q (same order), word 9 is splattedSamples.
         {
-            const uint32_t slot = warpPush(&qs.counters->raygenQueue, valid && terminate);
-            if (valid && terminate) qs.q[FLX_Q_RAYGEN][slot] = gid;
-        }
-        {
-            const uint32_t slot = warpPush(&qs.counters->shadowQueue, pushShadow);
-            if (pushShadow) qs.q[FLX_Q_SHADOW][slot] = gid;
-        }
-        if (!separate)
-        {
-            const uint32_t slot = warpPush(&qs.counters->diffuseQueue, matQ >= 0);
-            if (matQ >= 0) qs.q[FLX_Q_DIFFUSE][slot] = gid;
-        }
-        else
-        {
+            const unsigned FULL = 0xffffffffu;
+            const unsigned lane = threadIdx.x & 31u;
+            const int myQ = (valid && terminate) ? FLX_Q_RAYGEN : matQ; // a path is regenerated or shaded, never both
+            unsigned mine = 0u;                                          // ballot of the queue this lane reserves for
 #pragma unroll
-            for (int q = FLX_Q_DIFFUSE; q <= FLX_Q_EMISSIVE; q++)
+            for (int q = 0; q < FLX_NUM_QUEUES; q++)
             {
-                const uint32_t slot = warpPush(counterOf(qs.counters, q), matQ == q);
-                if (matQ == q) qs.q[q][slot] = gid;
+                if (q == FLX_Q_EXTENSION) continue;
+                if (!separate && q > FLX_Q_DIFFUSE) continue;
+                const unsigned m = __ballot_sync(FULL, q == FLX_Q_SHADOW ? pushShadow : (myQ == q));
+                if (lane == (unsigned)q) mine = m;
             }
-        }
-        if (checkSpp)
-        {
-            const unsigned m = __ballot_sync(0xffffffffu, splatted);
-            if ((threadIdx.x & 31u) == 0u && m) atomicAdd(&qs.counters->splattedSamples, (uint32_t)__popc(m));
+            const unsigned mSplat = checkSpp ? __ballot_sync(FULL, splatted) : 0u;
+            if (lane == 9u) mine = mSplat;
+            uint32_t base = 0u;
+            if (mine != 0u) base = atomicAdd(((uint32_t *)qs.counters) + lane, (uint32_t)__popc(mine));
+            const unsigned lt = (1u << lane) - 1u;
+            // every lane asks the reserving lane of its queue for the base and the mask (two shuffles per push)
+            const int srcA = myQ >= 0 ? myQ : 0;
+            const uint32_t baseA = __shfl_sync(FULL, base, srcA);
+            const unsigned maskA = __shfl_sync(FULL, mine, srcA);
+            if (myQ >= 0) (qs.q[0] + (size_t)myQ * N)[baseA + (uint32_t)__popc(maskA & lt)] = gid; // queues are contiguous, N apart
+            const uint32_t baseS = __shfl_sync(FULL, base, FLX_Q_SHADOW);
+            const unsigned maskS = __shfl_sync(FULL, mine, FLX_Q_SHADOW);
+            if (pushShadow) qs.q[FLX_Q_SHADOW][baseS + (uint32_t)__popc(maskS & lt)] = gid;
         }
     }
 }
@@ -271,7 +281,7 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
 // Shared body of the material stages (wf_mat_diffuse.cl:7-66 and its five siblings, wf_mat_all.cl).
 // TYPES is the compile-time set of BxDFs this instantiation can meet in its queue.
 template <int TYPES>
-__global__ void __launch_bounds__(FLX_WF_THREADS)
+__global__ void __launch_bounds__(FLX_WF_THREADS, FLX_MAT_MIN_BLOCKS)
 k_material(PathState st, Queues qs, MaterialsDev md, int queueId)
 {
     const uint32_t qlen = *counterOf(qs.counters, queueId);

@@ -58,9 +58,13 @@ int flx_repack_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, cons
                 const flx_triangle &t = tris[ti];
                 const int32_t last = (k + 1 == e) ? 1 : 0;
                 float4 *o = &hSlots[3 * k];
+                // v0 and the edges s1 = v1 - v0, s2 = v2 - v0 of intersect.cl:66-67: single IEEE binary32
+                // subtractions (volatile: no excess precision, no reassociation), identical to the device's FADD
+                volatile float e1x = t.v1.p.x - t.v0.p.x, e1y = t.v1.p.y - t.v0.p.y, e1z = t.v1.p.z - t.v0.p.z;
+                volatile float e2x = t.v2.p.x - t.v0.p.x, e2y = t.v2.p.y - t.v0.p.y, e2z = t.v2.p.z - t.v0.p.z;
                 o[0] = make_float4(t.v0.p.x, t.v0.p.y, t.v0.p.z, 0.f); memcpy(&o[0].w, &ti, 4);
-                o[1] = make_float4(t.v1.p.x, t.v1.p.y, t.v1.p.z, 0.f); memcpy(&o[1].w, &last, 4);
-                o[2] = make_float4(t.v2.p.x, t.v2.p.y, t.v2.p.z, 0.f); memcpy(&o[2].w, &t.matId, 4);
+                o[1] = make_float4(e1x, e1y, e1z, 0.f); memcpy(&o[1].w, &last, 4);
+                o[2] = make_float4(e2x, e2y, e2z, 0.f); memcpy(&o[2].w, &t.matId, 4);
             }
         }
     }

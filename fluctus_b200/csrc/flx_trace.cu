@@ -8,6 +8,9 @@
 #include "flx_internal.h"
 
 #define FLX_TRACE_THREADS 128
+#ifndef FLX_TRACE_MIN_BLOCKS
+#define FLX_TRACE_MIN_BLOCKS 1
+#endif
 
 FLX_DEV void flushCounts(unsigned long long *stats, const TravCount &c, unsigned int hits, unsigned int rays)
 {
@@ -150,7 +153,7 @@ struct AnyBatchJob
 };
 
 template <bool COUNT>
-__global__ void __launch_bounds__(FLX_TRACE_THREADS)
+__global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
       unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
 {
@@ -161,7 +164,7 @@ k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_qu
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(FLX_TRACE_THREADS)
+__global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
          unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
 {
@@ -172,7 +175,7 @@ k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(FLX_TRACE_THREADS)
+__global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
               int32_t *__restrict__ hitI, float *__restrict__ hitT, float4 *__restrict__ hits)
 {
@@ -183,7 +186,7 @@ k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsig
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(FLX_TRACE_THREADS)
+__global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_any_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
             uint8_t *__restrict__ occ)
 {
