@@ -61,7 +61,7 @@ FLX_DEV int materialQueueOf(int type, bool separate)
     return -1;
 }
 
-FLX_DEV uint32_t *counterOf(flx_queue_counters *c, int q) { return ((uint32_t *)c) + q; } // same order as FLX_Q_*
+static __host__ __device__ __forceinline__ uint32_t *counterOf(flx_queue_counters *c, int q) { return ((uint32_t *)c) + q; } // same order as FLX_Q_*
 
 __global__ void __launch_bounds__(FLX_WF_THREADS, FLX_LOGIC_MIN_BLOCKS)
 k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env, uint32_t N, uint32_t firstIteration,
@@ -282,11 +282,11 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
 // TYPES is the compile-time set of BxDFs this instantiation can meet in its queue.
 template <int TYPES>
 __global__ void __launch_bounds__(FLX_WF_THREADS, FLX_MAT_MIN_BLOCKS)
-k_material(PathState st, Queues qs, MaterialsDev md, int queueId)
+k_material(PathState st, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ queueLen,
+           uint32_t *__restrict__ extQueue, uint32_t *extCounter, MaterialsDev md)
 {
-    const uint32_t qlen = *counterOf(qs.counters, queueId);
+    const uint32_t qlen = *queueLen;
     const uint32_t rounded = (qlen + 31u) & ~31u;
-    const uint32_t *__restrict__ queue = qs.q[queueId];
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < rounded; k += gridDim.x * blockDim.x)
     {
         const bool valid = k < qlen;
@@ -322,8 +322,8 @@ k_material(PathState st, Queues qs, MaterialsDev md, int queueId)
             st.ray1[gid] = make_float4(newDir.x, newDir.y, newDir.z, r1.w);
             st.lastSpecular[gid] = FLX_BXDF_IS_SINGULAR(mat.type) ? 1u : 0u;
         }
-        const uint32_t slot = warpPush(&qs.counters->extensionQueue, valid);
-        if (valid) qs.q[FLX_Q_EXTENSION][slot] = gid;
+        const uint32_t slot = warpPush(extCounter, valid);
+        if (valid) extQueue[slot] = gid;
     }
 }
 
@@ -353,21 +353,21 @@ int flx_launch_materials(flx_ctx *ctx)
     const int grid = wfGrid(ctx, ctx->N);
     if (!ctx->params.wfSeparateQueues)
     {
-        k_material<FLX_ALL_TYPES><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_DIFFUSE);
+        k_material<FLX_ALL_TYPES><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_DIFFUSE], counterOf(ctx->qs.counters, FLX_Q_DIFFUSE), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
         FLX_LAUNCHED(ctx);
         return FLX_OK;
     }
-    k_material<FLX_BXDF_DIFFUSE><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_DIFFUSE);
+    k_material<FLX_BXDF_DIFFUSE><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_DIFFUSE], counterOf(ctx->qs.counters, FLX_Q_DIFFUSE), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
     FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_GLOSSY><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_GLOSSY);
+    k_material<FLX_BXDF_GLOSSY><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_GLOSSY], counterOf(ctx->qs.counters, FLX_Q_GLOSSY), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
     FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_GGX_ROUGH_REFLECTION><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_GGX_REFL);
+    k_material<FLX_BXDF_GGX_ROUGH_REFLECTION><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_GGX_REFL], counterOf(ctx->qs.counters, FLX_Q_GGX_REFL), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
     FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_GGX_ROUGH_DIELECTRIC><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_GGX_REFR);
+    k_material<FLX_BXDF_GGX_ROUGH_DIELECTRIC><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_GGX_REFR], counterOf(ctx->qs.counters, FLX_Q_GGX_REFR), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
     FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_IDEAL_REFLECTION | FLX_BXDF_IDEAL_DIELECTRIC><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_DELTA);
+    k_material<FLX_BXDF_IDEAL_REFLECTION | FLX_BXDF_IDEAL_DIELECTRIC><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_DELTA], counterOf(ctx->qs.counters, FLX_Q_DELTA), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
     FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_EMISSIVE><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->mats, FLX_Q_EMISSIVE);
+    k_material<FLX_BXDF_EMISSIVE><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_EMISSIVE], counterOf(ctx->qs.counters, FLX_Q_EMISSIVE), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
