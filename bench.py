@@ -138,7 +138,8 @@ class CpuWavefront:
         from oracle import pyoracle  # allowed here: cpu_baseline / --impl reference legs only
         from fluctus_b200 import abi, scene as fs
         self.po = pyoracle
-        self.threads = pyoracle.max_threads()
+        # all the host cores this process may use (torchrun exports OMP_NUM_THREADS=1, which is not the machine)
+        self.threads = max(pyoracle.max_threads(), len(os.sched_getaffinity(0)))
         pyoracle.set_threads(self.threads)
         self.wf = pyoracle.OracleWavefront(CPU_TASKS, WIDTH, HEIGHT)
         self.wf.set_scene(scene)
