@@ -27,7 +27,23 @@ struct DevBVH
     const float4 *slots;  // 3 per leaf slot
     const float4 *shade;  // 4 per triangle
     int rootRef;
+    int topN;             // inner nodes [0, topN) are the breadth-first top of the tree (staged in shared memory)
 };
+
+// Top of the tree in shared memory: FLX_TOP_NODES x 64 B per CTA, stored as four float4 planes (plane k holds
+// float4 k of every node) so that lanes reading different nodes spread over the banks.  880 nodes = 56 320 B,
+// one CTA of 1024 threads per SM (see flx_trace.cu).
+#ifndef FLX_TOP_NODES
+#define FLX_TOP_NODES 880
+#endif
+#define FLX_TOP_SMEM_BYTES (FLX_TOP_NODES * 64)
+
+FLX_DEV void stageTopNodes(const DevBVH &bvh, float4 *top)
+{
+    for (int e = threadIdx.x; e < 4 * bvh.topN; e += blockDim.x)
+        top[(e & 3) * FLX_TOP_NODES + (e >> 2)] = __ldg(bvh.nodes + e);
+    __syncthreads();
+}
 
 #define FLX_STACK_SIZE 64 // reference: uint stack[64] (src/bvh.cl:240)
 
@@ -102,7 +118,7 @@ struct TravCount { unsigned int inner, leaf, tri; };
 //     bool load(unsigned k, f3 &o, f3 &d, float &tmax)   // false: ray k needs no traversal (already resolved)
 //     void store(const RayHit &h, f3 o, f3 d)            // result of the ray loaded last by this lane
 #ifndef FLX_VOTE_RETIRE
-#define FLX_VOTE_RETIRE 8
+#define FLX_VOTE_RETIRE 12
 #endif
 #ifndef FLX_VOTE_LEAF
 #define FLX_VOTE_LEAF 8
@@ -115,8 +131,19 @@ struct TravCount { unsigned int inner, leaf, tri; };
 #endif
 #define FLX_TRAV_DONE ((int)0x80000000) // not a valid ref: leaf refs are ~slot with slot < 0x7fffffff
 
+// Hint the line holding the next node / leaf slot into L1 as soon as its address is known: the lane usually
+// waits at least one vote before it touches it.  No registers are held, and a wrong guess costs nothing.
+FLX_DEV void prefetchRef(const DevBVH &bvh, int ref)
+{
+#ifdef FLX_TRAV_PREFETCH
+    if (ref == FLX_TRAV_DONE) return;
+    const void *p = ref >= 0 ? (const void *)(bvh.nodes + 4 * (size_t)ref) : (const void *)(bvh.slots + 3 * (size_t)(~ref));
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#endif
+}
+
 template <bool ANY, bool COUNT, class Job>
-FLX_DEV void traceLoop(const DevBVH &bvh, Job &job, unsigned int *cursor, unsigned int total, TravCount &cnt)
+FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &job, unsigned int *cursor, unsigned int total, TravCount &cnt)
 {
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
@@ -189,6 +216,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, Job &job, unsigned int *cursor, unsign
                     if (ANY && found) cur = FLX_TRAV_DONE;
                     else if (__float_as_int(q1.w) != 0) cur = sp ? stack[--sp] : FLX_TRAV_DONE; // last slot of the leaf
                     else cur = cur - 1;                                                         // ~(slot + 1)
+                    prefetchRef(bvh, cur);
                 }
                 m = __ballot_sync(FULL, active && cur < 0 && cur != FLX_TRAV_DONE);
             } while (__popc(m) >= FLX_STAY_LEAF);
@@ -202,8 +230,16 @@ FLX_DEV void traceLoop(const DevBVH &bvh, Job &job, unsigned int *cursor, unsign
                 if (active && cur >= 0)
                 {
                     if (COUNT) cnt.inner++;
-                    const float4 *n = bvh.nodes + 4 * (size_t)cur;
-                    const float4 n0 = __ldg(n), n1 = __ldg(n + 1), n2 = __ldg(n + 2), n3 = __ldg(n + 3);
+                    float4 n0, n1, n2, n3;
+                    if (cur < bvh.topN)
+                    {
+                        n0 = top[cur]; n1 = top[FLX_TOP_NODES + cur]; n2 = top[2 * FLX_TOP_NODES + cur]; n3 = top[3 * FLX_TOP_NODES + cur];
+                    }
+                    else
+                    {
+                        const float4 *n = bvh.nodes + 4 * (size_t)cur;
+                        n0 = __ldg(n); n1 = __ldg(n + 1); n2 = __ldg(n + 2); n3 = __ldg(n + 3);
+                    }
                     float lnear, rnear;
                     const bool lh = slabTest(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, dinv, best.t, lnear);
                     const bool rh = slabTest(n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, o, dinv, best.t, rnear);
@@ -218,6 +254,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, Job &job, unsigned int *cursor, unsign
                     else if (rh) cur = r;
                     else cur = sp ? stack[--sp] : FLX_TRAV_DONE;
                     if (COUNT && cur < 0 && cur != FLX_TRAV_DONE) cnt.leaf++;
+                    prefetchRef(bvh, cur);
                 }
                 m = __ballot_sync(FULL, active && cur >= 0);
             } while (__popc(m) >= FLX_STAY_INNER);

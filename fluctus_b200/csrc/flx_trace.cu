@@ -7,7 +7,9 @@
 // triangle tests, hits, rays) for the algorithmic-bytes figure; they are never the timed ones.
 #include "flx_internal.h"
 
-#define FLX_TRACE_THREADS 128
+#ifndef FLX_TRACE_THREADS
+#define FLX_TRACE_THREADS 1024
+#endif
 #ifndef FLX_TRACE_MIN_BLOCKS
 #define FLX_TRACE_MIN_BLOCKS 1
 #endif
@@ -157,9 +159,13 @@ __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
       unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
 {
+    extern __shared__ float4 topNodes[];
+    const unsigned int total = counters->extensionQueue;
+    if (total == 0u) return;
+    stageTopNodes(bvh, topNodes);
     ExtJob job = {bvh, st, queue, params, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<false, COUNT>(bvh, job, cursor, counters->extensionQueue, cnt);
+    traceLoop<false, COUNT>(bvh, topNodes, job, cursor, total, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
@@ -168,9 +174,13 @@ __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
          unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
 {
+    extern __shared__ float4 topNodes[];
+    const unsigned int total = counters->shadowQueue;
+    if (total == 0u) return;
+    stageTopNodes(bvh, topNodes);
     ShadowJob job = {st, queue, params, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<true, COUNT>(bvh, job, cursor, counters->shadowQueue, cnt);
+    traceLoop<true, COUNT>(bvh, topNodes, job, cursor, total, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
@@ -179,9 +189,11 @@ __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
               int32_t *__restrict__ hitI, float *__restrict__ hitT, float4 *__restrict__ hits)
 {
+    extern __shared__ float4 topNodes[];
+    stageTopNodes(bvh, topNodes);
     BatchJob job = {bvh, rays, hitI, hitT, hits, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<false, COUNT>(bvh, job, cursor, n, cnt);
+    traceLoop<false, COUNT>(bvh, topNodes, job, cursor, n, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
@@ -190,14 +202,35 @@ __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_any_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
             uint8_t *__restrict__ occ)
 {
+    extern __shared__ float4 topNodes[];
+    stageTopNodes(bvh, topNodes);
     AnyBatchJob job = {rays, occ, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<true, COUNT>(bvh, job, cursor, n, cnt);
+    traceLoop<true, COUNT>(bvh, topNodes, job, cursor, n, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
 // ---------------------------------------------------------------------------------------------
-static int traceGrid(const flx_ctx *ctx) { return ctx->numSMs * 8; }
+// One persistent CTA of 1024 threads per SM: a single 55 KB copy of the top of the tree per SM.  Smaller CTAs
+// need one copy each, and the shared-memory carve-out then eats the L1 the deeper nodes and the triangles live
+// in (8 x 28 KB copies cost 8 % on the kitchen render and 17 % on incoherent rays; tools/tune_vote.sh).
+static int traceGrid(const flx_ctx *ctx) { return ctx->numSMs * (1024 / FLX_TRACE_THREADS); }
+
+// dynamic shared memory above 48 KB has to be opted into, once per kernel
+static cudaError_t traceKernelSetup()
+{
+    static bool done = false;
+    if (done) return cudaSuccess;
+    const void *kernels[] = {(const void *)k_ext<false>, (const void *)k_ext<true>, (const void *)k_shadow<false>, (const void *)k_shadow<true>,
+                             (const void *)k_trace_batch<false>, (const void *)k_trace_batch<true>, (const void *)k_any_batch<false>, (const void *)k_any_batch<true>};
+    for (const void *k : kernels)
+    {
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FLX_TOP_SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+    }
+    done = true;
+    return cudaSuccess;
+}
 
 // cursors live right behind the pixel cursor: [1] ext, [2] shadow / batch
 static unsigned int *workCursor(flx_ctx *ctx, int which) { return (unsigned int *)(ctx->dPixelIdx + 1 + which); }
@@ -206,24 +239,26 @@ static unsigned int *workCursor(flx_ctx *ctx, int which) { return (unsigned int 
 
 int flx_launch_ext(flx_ctx *ctx)
 {
+    FLX_CUDA(ctx, traceKernelSetup());
     unsigned int *cur = workCursor(ctx, 0);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
-        k_ext<true><<<traceGrid(ctx), FLX_TRACE_THREADS, 0, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, ctx->dTraceStats, ctx->params);
+        k_ext<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, ctx->dTraceStats, ctx->params);
     else
-        k_ext<false><<<traceGrid(ctx), FLX_TRACE_THREADS, 0, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, nullptr, ctx->params);
+        k_ext<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, nullptr, ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
 
 int flx_launch_shadow(flx_ctx *ctx)
 {
+    FLX_CUDA(ctx, traceKernelSetup());
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
-        k_shadow<true><<<traceGrid(ctx), FLX_TRACE_THREADS, 0, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, ctx->dTraceStats + 5, ctx->params);
+        k_shadow<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, ctx->dTraceStats + 5, ctx->params);
     else
-        k_shadow<false><<<traceGrid(ctx), FLX_TRACE_THREADS, 0, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, nullptr, ctx->params);
+        k_shadow<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, nullptr, ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
@@ -232,12 +267,13 @@ int flx_launch_trace_batch(flx_ctx *ctx, const float4 *dRays, size_t n, int32_t 
 {
     if (n == 0) return FLX_OK;
     if (n > 0xfffffff0u) return flx_fail(ctx, FLX_ERR_ARG, "ray batch too large");
+    FLX_CUDA(ctx, traceKernelSetup());
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
-        k_trace_batch<true><<<traceGrid(ctx), FLX_TRACE_THREADS, 0, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 10, dHitI, dHitT, (float4 *)dHits);
+        k_trace_batch<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 10, dHitI, dHitT, (float4 *)dHits);
     else
-        k_trace_batch<false><<<traceGrid(ctx), FLX_TRACE_THREADS, 0, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dHitI, dHitT, (float4 *)dHits);
+        k_trace_batch<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dHitI, dHitT, (float4 *)dHits);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
@@ -246,12 +282,13 @@ int flx_launch_any_batch(flx_ctx *ctx, const float4 *dRays, size_t n, uint8_t *d
 {
     if (n == 0) return FLX_OK;
     if (n > 0xfffffff0u) return flx_fail(ctx, FLX_ERR_ARG, "ray batch too large");
+    FLX_CUDA(ctx, traceKernelSetup());
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
-        k_any_batch<true><<<traceGrid(ctx), FLX_TRACE_THREADS, 0, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 15, dOcc);
+        k_any_batch<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 15, dOcc);
     else
-        k_any_batch<false><<<traceGrid(ctx), FLX_TRACE_THREADS, 0, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dOcc);
+        k_any_batch<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dOcc);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }

@@ -6,8 +6,11 @@
 
 using namespace orc;
 
+namespace orc { extern uint32_t *g_nodeVisitHistogram; } // o_trace.cpp
+
 extern "C" {
 
+void orc_set_node_histogram(uint32_t *hist) { orc::g_nodeVisitHistogram = hist; } // nullptr switches it off
 void orc_set_threads(int n) { omp_set_num_threads(n > 0 ? n : 1); }
 int orc_max_threads() { return omp_get_max_threads(); }
 

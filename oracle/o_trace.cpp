@@ -131,6 +131,10 @@ static inline bool leafAny(const Ray &r, float maxDist, const SceneView &s, uint
 }
 
 // reference src/bvh.cl:234-310 (stack variant — the default, settings.cpp:27)
+// Optional per-node visit histogram (analysis aid for DESIGN.md: which share of the inner-node visits falls on
+// the top levels of the tree).  Not thread-safe: use with one thread.
+uint32_t *g_nodeVisitHistogram = nullptr;
+
 void bvhIntersectStack(const Ray &r, Hit *hit, const SceneView &s, TraceCounters *c)
 {
     float lnear, lfar, rnear, rfar;
@@ -149,6 +153,7 @@ void bvhIntersectStack(const Ray &r, Hit *hit, const SceneView &s, TraceCounters
         else
         {
             if (c) c->inner_visits++;
+            if (g_nodeVisitHistogram) g_nodeVisitHistogram[ni]++;
             const uint32_t li = ni + 1, ri = n.iStartOrRight;
             const bool lh = intersectAABB(r, s.nodes[li].bmin, s.nodes[li].bmax, &lnear, &lfar, hit->t);
             const bool rh = intersectAABB(r, s.nodes[ri].bmin, s.nodes[ri].bmax, &rnear, &rfar, hit->t);

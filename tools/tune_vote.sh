@@ -4,7 +4,7 @@
 cd "$(dirname "$0")/.."
 for cfg in "$@"; do
   set -- $cfg
-  touch fluctus_b200/csrc/flx_trace.cu fluctus_b200/csrc/flx_logic.cu
+  touch fluctus_b200/csrc/flx_trace.cu fluctus_b200/csrc/flx_logic.cu fluctus_b200/csrc/flx_repack.cu
   make -s -C fluctus_b200/csrc EXTRA="-DFLX_VOTE_RETIRE=$1 -DFLX_VOTE_LEAF=$2 -DFLX_STAY_LEAF=$3 -DFLX_STAY_INNER=$4 $EXTRA_DEFS" || exit 1
   python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>/dev/null | python -c "
 import json,sys
