@@ -5,7 +5,7 @@
 
 #define FLX_WF_THREADS 256
 #ifndef FLX_LOGIC_MIN_BLOCKS
-#define FLX_LOGIC_MIN_BLOCKS 1
+#define FLX_LOGIC_MIN_BLOCKS 4
 #endif
 #ifndef FLX_MAT_MIN_BLOCKS
 #define FLX_MAT_MIN_BLOCKS 1
