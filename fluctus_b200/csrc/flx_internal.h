@@ -92,6 +92,7 @@ struct flx_ctx
     MaterialsDev mats{}; flx_material *dMaterials = nullptr; flx_tex_desc *dTextures = nullptr; uint8_t *dTexels = nullptr;
     flx_triangle *dTris160 = nullptr;
     bool sceneReady = false;
+    bool traceSetupDone = false; // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) done on this device
     EnvMapDev env{}; float4 *dEnv = nullptr; float *dProb = nullptr, *dPdf = nullptr; int *dAlias = nullptr;
 
     // wavefront

@@ -3,6 +3,7 @@
 #include "flx_internal.h"
 #include <cstring>
 #include <cstdlib>
+#include <utility>
 
 // ---------------------------------------------------------------------------------------------
 // Re-pack the reference's Node[48 B] / RTTriangle[160 B] / indices into the streams described in
@@ -39,6 +40,27 @@ int flx_repack_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, cons
     }
     for (size_t i = 0; i < n_nodes; i++)
         if (nodes[i].nPrims == 0 && innerIndex[i] < 0) innerIndex[i] = (int32_t)nInner++;
+
+    // The traversal stack holds one entry per level at most (the far child of every ancestor): the reference
+    // uses uint stack[64] unchecked (src/bvh.cl:240); here a deeper tree is refused at upload.
+    {
+        std::vector<std::pair<uint32_t, uint32_t>> todo(1, std::make_pair(0u, 1u));
+        uint32_t maxDepth = 0;
+        size_t visited = 0;
+        while (!todo.empty())
+        {
+            const std::pair<uint32_t, uint32_t> it = todo.back(); todo.pop_back();
+            if (++visited > n_nodes) return flx_fail(ctx, FLX_ERR_ARG, "flx_upload_scene: node array is not a tree");
+            if (it.second > maxDepth) maxDepth = it.second;
+            const flx_node &n = nodes[it.first];
+            if (n.nPrims != 0) continue;
+            const size_t li = (size_t)it.first + 1, ri = n.iStartOrRight;
+            if (li >= n_nodes || ri >= n_nodes) return flx_fail(ctx, FLX_ERR_ARG, "flx_upload_scene: child index out of range");
+            todo.push_back(std::make_pair((uint32_t)li, it.second + 1));
+            todo.push_back(std::make_pair((uint32_t)ri, it.second + 1));
+        }
+        if (maxDepth > FLX_STACK_SIZE) return flx_fail(ctx, FLX_ERR_ARG, "flx_upload_scene: hierarchy deeper than the 64-entry traversal stack");
+    }
 
     auto refOf = [&](size_t child) -> int32_t {
         const flx_node &c = nodes[child];

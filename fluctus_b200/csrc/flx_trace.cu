@@ -216,11 +216,10 @@ k_any_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigne
 // in (8 x 28 KB copies cost 8 % on the kitchen render and 17 % on incoherent rays; tools/tune_vote.sh).
 static int traceGrid(const flx_ctx *ctx) { return ctx->numSMs * (1024 / FLX_TRACE_THREADS); }
 
-// dynamic shared memory above 48 KB has to be opted into, once per kernel
-static cudaError_t traceKernelSetup()
+// dynamic shared memory above 48 KB has to be opted into, per kernel and per device
+static cudaError_t traceKernelSetup(flx_ctx *ctx)
 {
-    static bool done = false;
-    if (done) return cudaSuccess;
+    if (ctx->traceSetupDone) return cudaSuccess;
     const void *kernels[] = {(const void *)k_ext<false>, (const void *)k_ext<true>, (const void *)k_shadow<false>, (const void *)k_shadow<true>,
                              (const void *)k_trace_batch<false>, (const void *)k_trace_batch<true>, (const void *)k_any_batch<false>, (const void *)k_any_batch<true>};
     for (const void *k : kernels)
@@ -228,7 +227,7 @@ static cudaError_t traceKernelSetup()
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FLX_TOP_SMEM_BYTES);
         if (e != cudaSuccess) return e;
     }
-    done = true;
+    ctx->traceSetupDone = true;
     return cudaSuccess;
 }
 
@@ -239,7 +238,7 @@ static unsigned int *workCursor(flx_ctx *ctx, int which) { return (unsigned int 
 
 int flx_launch_ext(flx_ctx *ctx)
 {
-    FLX_CUDA(ctx, traceKernelSetup());
+    FLX_CUDA(ctx, traceKernelSetup(ctx));
     unsigned int *cur = workCursor(ctx, 0);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
@@ -252,7 +251,7 @@ int flx_launch_ext(flx_ctx *ctx)
 
 int flx_launch_shadow(flx_ctx *ctx)
 {
-    FLX_CUDA(ctx, traceKernelSetup());
+    FLX_CUDA(ctx, traceKernelSetup(ctx));
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
@@ -267,7 +266,7 @@ int flx_launch_trace_batch(flx_ctx *ctx, const float4 *dRays, size_t n, int32_t 
 {
     if (n == 0) return FLX_OK;
     if (n > 0xfffffff0u) return flx_fail(ctx, FLX_ERR_ARG, "ray batch too large");
-    FLX_CUDA(ctx, traceKernelSetup());
+    FLX_CUDA(ctx, traceKernelSetup(ctx));
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
@@ -282,7 +281,7 @@ int flx_launch_any_batch(flx_ctx *ctx, const float4 *dRays, size_t n, uint8_t *d
 {
     if (n == 0) return FLX_OK;
     if (n > 0xfffffff0u) return flx_fail(ctx, FLX_ERR_ARG, "ray batch too large");
-    FLX_CUDA(ctx, traceKernelSetup());
+    FLX_CUDA(ctx, traceKernelSetup(ctx));
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)

@@ -126,3 +126,39 @@ def test_empty_batch_and_errors(ctx, teapot):
     with pytest.raises(FluctusError):
         ctx.uploadSceneData(bad)
     ctx.uploadSceneData(teapot)  # context stays usable after a rejected upload
+
+
+def _chain_scene(teapot, levels):
+    """Degenerate hierarchy: every inner node has a one-triangle leaf on the left and the rest of the chain on
+    the right — depth = levels + 1.  Obeys the reference's Node[] invariants."""
+    from fluctus_b200.abi import NODE_DT
+    tris = teapot["tris"][:levels + 1].copy()
+    P = tris["v"][:, :, 0, :3]
+    nodes = np.zeros(2 * levels + 1, NODE_DT)
+    lo = np.minimum.accumulate(P.min(1)[::-1])[::-1]   # box of triangles k..end
+    hi = np.maximum.accumulate(P.max(1)[::-1])[::-1]
+    for k in range(levels):
+        inner, leaf = 2 * k, 2 * k + 1
+        nodes[inner]["bmin"][:3], nodes[inner]["bmax"][:3] = lo[k], hi[k]
+        nodes[inner]["parent"], nodes[inner]["iStartOrRight"], nodes[inner]["nPrims"] = (2 * (k - 1) if k else -1), 2 * k + 2, 0
+        nodes[leaf]["bmin"][:3], nodes[leaf]["bmax"][:3] = P[k].min(0), P[k].max(0)
+        nodes[leaf]["parent"], nodes[leaf]["iStartOrRight"], nodes[leaf]["nPrims"] = inner, k, 1
+    last = 2 * levels
+    nodes[last]["bmin"][:3], nodes[last]["bmax"][:3] = P[levels].min(0), P[levels].max(0)
+    nodes[last]["parent"], nodes[last]["iStartOrRight"], nodes[last]["nPrims"] = 2 * (levels - 1), levels, 1
+    scene = dict(teapot, tris=tris, nodes=nodes, indices=np.arange(levels + 1, dtype=np.uint32))
+    scene["bounds"] = np.stack([lo[0], hi[0]])
+    return scene
+
+
+def test_deep_chain_hierarchy(ctx, oracle, teapot):
+    """Depth 61 (within the 64-entry stack, deeper than the shared-memory top levels are wide) traverses
+    bit-exactly; depth 71 is refused at upload instead of overflowing the stack (reference: unchecked)."""
+    from fluctus_b200 import FluctusError
+    scene = _chain_scene(teapot, 60)
+    rays = _rays_inside(scene, 8192, 9)
+    _check_closest(ctx, oracle, scene, rays)
+    with pytest.raises(FluctusError) as e:
+        ctx.uploadSceneData(_chain_scene(teapot, 70))
+    assert "deeper" in str(e.value)
+    ctx.uploadSceneData(teapot)
