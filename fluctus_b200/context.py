@@ -89,6 +89,10 @@ class CudaContext:
     def setOptions(self, denoiser_aov=False, seed_offset=0):
         self._check(self.L.flx_set_options(self.h, int(denoiser_aov), int(seed_offset)))
 
+    def setPixelSharding(self, rank, world):
+        """Preview sharding: this context traces only the image rows y % world == rank (world=1: off)."""
+        self._check(self.L.flx_set_pixel_sharding(self.h, int(rank), int(world)))
+
     def recompileKernels(self, setArgs=False):
         """No-op: every specialisation is compiled ahead of time and picked by updateParams."""
 

@@ -233,6 +233,16 @@ int flx_set_options(flx_ctx *ctx, int denoiser_aov, uint32_t seed_offset)
     return FLX_OK;
 }
 
+int flx_set_pixel_sharding(flx_ctx *ctx, uint32_t rank, uint32_t world)
+{
+    FLX_CHECK_CTX(ctx);
+    if (world == 0 || rank >= world) return flx_fail(ctx, FLX_ERR_ARG, "flx_set_pixel_sharding: rank outside world");
+    if (ctx->paramsSet && world > ctx->params.height) return flx_fail(ctx, FLX_ERR_ARG, "flx_set_pixel_sharding: more ranks than image rows");
+    if (ctx->tileRank != rank || ctx->tileWorld != world) invalidateGraph(ctx);
+    ctx->tileRank = rank; ctx->tileWorld = world;
+    return FLX_OK;
+}
+
 int flx_set_pixel_index(flx_ctx *ctx, uint32_t value)
 {
     FLX_CHECK_CTX(ctx);

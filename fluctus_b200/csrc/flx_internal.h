@@ -103,6 +103,7 @@ struct flx_ctx
     FrameBuffers fb{}; void *fbBlock = nullptr;
     flx_render_params params{}; bool paramsSet = false;
     int denoiserAOV = 0; uint32_t seedOffset = 0;
+    uint32_t tileRank = 0, tileWorld = 1; // preview sharding: rows y % tileWorld == tileRank belong to this context
     flx_queue_counters *hCounters = nullptr; // pinned staging for async counter reads
     std::vector<flx_queue_counters *> pendingCounterReads;
 
@@ -149,6 +150,13 @@ int flx_launch_bookkeeping(flx_ctx *ctx); // counters -> totals, pixel cursor ad
 int flx_launch_advance_pixel(flx_ctx *ctx, uint32_t numPixels, uint32_t numNew);
 int flx_launch_export_state(flx_ctx *ctx, uint32_t *dSlots64xN);
 int flx_launch_import_state(flx_ctx *ctx, const uint32_t *dSlots64xN);
+
+// pixels this context generates paths for (all of them unless preview sharding is on)
+static inline uint32_t flx_owned_pixels(const flx_ctx *ctx)
+{
+    if (ctx->tileWorld <= 1u) return ctx->fb.numPixels;
+    return ((ctx->params.height - ctx->tileRank + ctx->tileWorld - 1u) / ctx->tileWorld) * ctx->params.width;
+}
 
 // implemented in flx_context.cu
 int flx_ready(flx_ctx *ctx, bool needScene);

@@ -65,7 +65,8 @@ k_reset(PathState st, Queues qs, FrameBuffers fb, uint32_t N, uint32_t seedOffse
 
 // wf_raygen.cl:4-100
 __global__ void __launch_bounds__(FLX_WF_THREADS)
-k_raygen(PathState st, Queues qs, const uint32_t *__restrict__ currPixelIdx, const __grid_constant__ flx_render_params params)
+k_raygen(PathState st, Queues qs, const uint32_t *__restrict__ currPixelIdx, uint32_t tileRank, uint32_t tileWorld,
+         const __grid_constant__ flx_render_params params)
 {
     const uint32_t qlen = qs.counters->raygenQueue;
     const uint32_t rounded = (qlen + 31u) & ~31u;
@@ -80,7 +81,13 @@ k_raygen(PathState st, Queues qs, const uint32_t *__restrict__ currPixelIdx, con
         {
             gid = qs.q[FLX_Q_RAYGEN][k];
             uint32_t seed = __float_as_uint(st.thr[gid].w);
-            const uint32_t pixelIdx = (cursor + k) % numPixels;
+            uint32_t pixelIdx = (cursor + k) % numPixels; // wf_raygen.cl:25
+            if (tileWorld > 1u) // preview sharding: this rank owns the image rows y % tileWorld == tileRank
+            {
+                const uint32_t ownedRows = (params.height - tileRank + tileWorld - 1u) / tileWorld;
+                const uint32_t j = (cursor + k) % (ownedRows * params.width);
+                pixelIdx = ((j / params.width) * tileWorld + tileRank) * params.width + (j % params.width);
+            }
 
             float x = (float)(pixelIdx % params.width);
             float y = (float)(pixelIdx) * params.width1; // deliberately not floored, as the reference
@@ -250,7 +257,7 @@ int flx_launch_reset(flx_ctx *ctx)
 
 int flx_launch_raygen(flx_ctx *ctx)
 {
-    k_raygen<<<wfGrid(ctx, ctx->N), FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->dPixelIdx, ctx->params);
+    k_raygen<<<wfGrid(ctx, ctx->N), FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->dPixelIdx, ctx->tileRank, ctx->tileWorld, ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
@@ -264,7 +271,7 @@ int flx_launch_postprocess(flx_ctx *ctx)
 
 int flx_launch_bookkeeping(flx_ctx *ctx)
 {
-    k_bookkeeping<<<1, 1, 0, ctx->stream>>>(ctx->qs.counters, ctx->dTotals, ctx->dPixelIdx, ctx->fb.numPixels);
+    k_bookkeeping<<<1, 1, 0, ctx->stream>>>(ctx->qs.counters, ctx->dTotals, ctx->dPixelIdx, flx_owned_pixels(ctx));
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }

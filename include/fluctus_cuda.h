@@ -75,6 +75,12 @@ int flx_update_params(flx_ctx *ctx, const flx_render_params *params);
  * per-rank RNG offset used when samples are sharded over GPUs (seed = gid + seed_offset). */
 int flx_set_options(flx_ctx *ctx, int denoiser_aov, uint32_t seed_offset);
 
+/* Preview / single-spp sharding over GPUs (no reference counterpart): with world > 1 this context
+ * generates camera paths only for the image rows y % world == rank, so every rank refines its own interleaved
+ * slice of the frame and the slices are combined with one all-gather (or the same all-reduce: foreign rows stay
+ * zero).  world = 1 (default) restores the reference's pixel order (wf_raygen.cl:25). */
+int flx_set_pixel_sharding(flx_ctx *ctx, uint32_t rank, uint32_t world);
+
 /* CLContext::resetPixelIndex / updatePixelIndex (clcontext.cpp:917-927) */
 int flx_reset_pixel_index(flx_ctx *ctx);
 int flx_set_pixel_index(flx_ctx *ctx, uint32_t value);

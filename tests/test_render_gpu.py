@@ -116,3 +116,37 @@ def test_linearity_of_exposure(teapot, night_env):
     b = tr.preview()
     assert np.allclose(b[..., :3], 2.0 * a[..., :3], rtol=1e-6, atol=0)
     tr.close()
+
+
+def test_preview_row_sharding(teapot, night_env):
+    """SURVEY.md 8(e) preview mode: with flx_set_pixel_sharding(rank, world) a context generates camera paths only
+    for the rows y % world == rank; the slices of the ranks tile the frame and their sum is an unbiased frame."""
+    from fluctus_b200 import Tracer
+    W, H, G = 96, 50, 3  # 50 rows over 3 ranks: 17 + 17 + 16
+    frames = []
+    for r in range(G):
+        tr = Tracer(W, H, num_tasks=4096, rank=r, world_size=G, max_bounces=3, use_env_map=True, use_area_light=False)
+        tr.init(teapot, night_env)
+        tr.clctx.setPixelSharding(r, G)
+        tr.clctx.setPixelIndex(0)
+        tr.clctx.render(0, reset=True)
+        tr.clctx.render(120)
+        px = tr.pixels()
+        rows = np.arange(H) % G == r
+        assert px[~rows, :, 3].sum() == 0.0, "rank %d splatted outside its rows" % r
+        assert px[rows, :, 3].min() > 0
+        frames.append(px)
+        tr.close()
+    full = sum(frames)
+    assert full[..., 3].min() > 0
+    ref = Tracer(W, H, num_tasks=4096, max_bounces=3, use_env_map=True, use_area_light=False)
+    ref.init(teapot, night_env)
+    ref.render(iterations=360)
+    pr = ref.pixels()
+    ref.close()
+    a = (full[..., :3] / full[..., 3:])[:48].reshape(6, 8, 12, 8, 3).mean((1, 3))
+    b = (pr[..., :3] / np.maximum(pr[..., 3:], 1))[:48].reshape(6, 8, 12, 8, 3).mean((1, 3))
+    assert float((((a - b) ** 2) / (b ** 2 + 1e-3)).mean()) < 0.05
+    with pytest.raises(Exception):
+        ref2 = Tracer(W, H, num_tasks=64)
+        ref2.clctx.setPixelSharding(3, 3)
