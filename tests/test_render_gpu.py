@@ -150,3 +150,66 @@ def test_preview_row_sharding(teapot, night_env):
     with pytest.raises(Exception):
         ref2 = Tracer(W, H, num_tasks=64)
         ref2.clctx.setPixelSharding(3, 3)
+
+
+def _material_mix_scene():
+    """BASELINE config 2 stand-in (luxball.obj is stripped): psor-cube geometry with GGX rough reflection / rough
+    dielectric, ideal dielectric, mirror, glossy and diffuse materials assigned by triangle id."""
+    from conftest import cached_scene
+    from fluctus_b200 import abi
+    base = cached_scene("psor_cube")
+    scene = dict(base)
+    mats = np.tile(base["materials"][:1], 6)
+    types = [abi.BXDF_DIFFUSE, abi.BXDF_GLOSSY, abi.BXDF_GGX_ROUGH_REFLECTION, abi.BXDF_IDEAL_REFLECTION,
+             abi.BXDF_GGX_ROUGH_DIELECTRIC, abi.BXDF_IDEAL_DIELECTRIC]
+    for k, t in enumerate(types):
+        mats[k]["type"] = t
+        mats[k]["Kd"][:3] = (0.7, 0.45 + 0.05 * k, 0.3)
+        mats[k]["Ks"][:3] = (0.9, 0.85, 0.8)
+        mats[k]["Ns"], mats[k]["Ni"] = 0.12 + 0.04 * k, 1.5
+    tris = base["tris"].copy()
+    tris["matId"] = (np.arange(len(tris)) // 256) % 6
+    scene.update(materials=mats, tris=tris)
+    b = base["bounds"]
+    c = 0.5 * (b[0] + b[1])
+    view = dict(cam_pos=(float(c[0]), float(c[1]), float(b[1][2] + 1.2 * (b[1][2] - b[0][2]))),
+                light_pos=(float(c[0]) + 2.0, float(b[1][1]) + 1.0, float(c[2])))
+    return scene, view
+
+
+@pytest.mark.parametrize("which", ["material_mix", "egyptcat_textured", "kitchen_small"])
+def test_converged_image_material_scenes(oracle, teapot, night_env, which):
+    """Image-level parity on the stand-ins of BASELINE configs 2-4: every BxDF class, textures, the kitchen's
+    material mix, env-map MIS + area light, separate material queues, 8 bounces."""
+    from conftest import cached_scene
+    from fluctus_b200 import Tracer, abi, scene as fs
+    from fluctus_b200.standin import kitchen_standin
+    if which == "material_mix":
+        scene, view = _material_mix_scene()
+    elif which == "egyptcat_textured":
+        scene = cached_scene("egyptcat")
+        b = scene["bounds"]
+        c = 0.5 * (b[0] + b[1])
+        view = dict(cam_pos=(float(c[0]), float(c[1]), float(b[1][2] + 1.5 * (b[1][2] - b[0][2]))),
+                    light_pos=(float(c[0]) + 1.0, float(b[1][1]) + 1.0, float(c[2])))
+    else:
+        scene, view = kitchen_standin(teapot, grid=(3, 2, 2))
+    W = H = 64
+    N, iters = 8192, 500
+    kw = dict(max_bounces=8, use_env_map=True, use_area_light=True, separate_queues=True, **view)
+    p = abi.make_render_params(W, H, n_tris=len(scene["tris"]), world_radius=fs.world_radius(scene), **kw)
+    wf = oracle.OracleWavefront(N, W, H)
+    wf.set_scene(scene); wf.set_envmap(night_env); wf.set_params(p.tobytes())
+    done, st = wf.render(iters)
+    ref = _normalised(wf.pixels().reshape(H, W, 4))
+    tr = Tracer(W, H, num_tasks=N, **kw)
+    tr.init(scene, night_env)
+    tot = tr.render(iterations=iters)
+    img = _normalised(tr.pixels())
+    tr.close()
+    for k in ("primary", "extension", "shadow", "samples"):
+        assert abs(tot[k] - st[k]) <= 0.02 * st[k] + 64, (k, tot[k], st[k])
+    assert not np.isnan(img).any()
+    a, b = _block_means(img, 8), _block_means(ref, 8)
+    relmse = float((((a - b) ** 2) / (b ** 2 + 1e-3)).mean())
+    assert relmse < 0.03, relmse
