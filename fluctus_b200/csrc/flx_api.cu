@@ -37,6 +37,7 @@ int ensureScratch(flx_ctx *ctx, size_t bytes)
 }
 
 int stageLogic(flx_ctx *ctx, int first) { TimerScope t(ctx, 2); return flx_launch_logic(ctx, first); }
+int stageLogicRegen(flx_ctx *ctx) { TimerScope t(ctx, 2); return flx_launch_logic_regen(ctx); }
 int stageRaygen(flx_ctx *ctx) { TimerScope t(ctx, 3); return flx_launch_raygen(ctx); }
 int stageMaterials(flx_ctx *ctx) { TimerScope t(ctx, 4); return flx_launch_materials(ctx); }
 int stageExt(flx_ctx *ctx) { TimerScope t(ctx, 0); return flx_launch_ext(ctx); }
@@ -45,8 +46,7 @@ int stageShadow(flx_ctx *ctx) { TimerScope t(ctx, 1); return flx_launch_shadow(c
 // one pass of the reference's benchmark inner loop (tracer.cpp:737-778)
 int enqueueIteration(flx_ctx *ctx)
 {
-    FLX_TRY(stageLogic(ctx, 0));
-    FLX_TRY(stageRaygen(ctx));
+    FLX_TRY(stageLogicRegen(ctx)); // logic + raygen: terminated paths restart inside the logic kernel
     FLX_TRY(stageMaterials(ctx));
     FLX_TRY(stageExt(ctx));
     FLX_TRY(stageShadow(ctx));
@@ -138,7 +138,8 @@ int flx_render(flx_ctx *ctx, uint32_t iterations, int do_reset)
         FLX_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
         const uint64_t before = ctx->launches;
         const int rc = enqueueIteration(ctx);
-        ctx->launches = before; // capture enqueues nothing
+        ctx->graphKernels = ctx->launches - before; // kernels in one iteration
+        ctx->launches = before;                     // capture enqueues nothing
         cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
         if (rc != FLX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
         if (e != cudaSuccess) return flx_fail(ctx, FLX_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
@@ -147,11 +148,10 @@ int flx_render(flx_ctx *ctx, uint32_t iterations, int do_reset)
         if (e != cudaSuccess) return flx_fail(ctx, FLX_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
         ctx->graphValid = true;
     }
-    const uint64_t perIter = 6 + (ctx->params.wfSeparateQueues ? 5 : 0); // kernels in one iteration
     for (uint32_t i = 0; i < iterations; i++)
     {
         FLX_CUDA(ctx, cudaGraphLaunch(ctx->graphExec, ctx->stream));
-        ctx->launches += perIter;
+        ctx->launches += ctx->graphKernels;
     }
     return FLX_OK;
 }

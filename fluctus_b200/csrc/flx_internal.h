@@ -108,7 +108,7 @@ struct flx_ctx
     std::vector<flx_queue_counters *> pendingCounterReads;
 
     // graph for flx_render
-    cudaGraphExec_t graphExec = nullptr; bool graphValid = false;
+    cudaGraphExec_t graphExec = nullptr; bool graphValid = false; uint64_t graphKernels = 0;
 
     // timing
     bool timing = false; StageTimer timers[6];
@@ -144,6 +144,7 @@ int flx_launch_any_batch(flx_ctx *ctx, const float4 *dRays, size_t n, uint8_t *d
 int flx_launch_reset(flx_ctx *ctx);
 int flx_launch_raygen(flx_ctx *ctx);
 int flx_launch_logic(flx_ctx *ctx, int firstIteration);
+int flx_launch_logic_regen(flx_ctx *ctx);
 int flx_launch_materials(flx_ctx *ctx);
 int flx_launch_postprocess(flx_ctx *ctx);
 int flx_launch_bookkeeping(flx_ctx *ctx); // counters -> totals, pixel cursor advance, clear

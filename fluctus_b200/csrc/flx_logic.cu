@@ -2,6 +2,7 @@
 // compaction) and the material-queue shaders.
 // Behavioural contract: reference src/wf_logic.cl:14-344 and src/wf_mat_*.cl (identical bodies).
 #include "flx_bxdf.cuh"
+#include "flx_raygen.cuh"
 
 #define FLX_WF_THREADS 256
 #ifndef FLX_LOGIC_MIN_BLOCKS
@@ -63,9 +64,16 @@ FLX_DEV int materialQueueOf(int type, bool separate)
 
 static __host__ __device__ __forceinline__ uint32_t *counterOf(flx_queue_counters *c, int q) { return ((uint32_t *)c) + q; } // same order as FLX_Q_*
 
+// REGEN = true is the render entry's variant (flx_render): a terminated path is restarted in place — the body
+// of the raygen stage runs on the lane that just splatted, with the seed still in a register, and the path
+// goes straight into the extension queue — which saves the raygen launch and one round trip of thr/acc
+// through HBM.  The raygen-queue counter is still advanced (bookkeeping derives the sample count and the
+// pixel cursor from it) and a path's raygen-queue position still selects its pixel, as in wf_raygen.cl:25.
+template <bool REGEN>
 __global__ void __launch_bounds__(FLX_WF_THREADS, FLX_LOGIC_MIN_BLOCKS)
 k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env, uint32_t N, uint32_t firstIteration,
-        int denoiserAOV, const __grid_constant__ flx_render_params params)
+        int denoiserAOV, const uint32_t *__restrict__ currPixelIdx, uint32_t tileRank, uint32_t tileWorld,
+        const __grid_constant__ flx_render_params params)
 {
     const uint32_t numPixels = params.width * params.height;
     const uint32_t maxId = firstIteration ? min(numPixels, N) : N;
@@ -78,13 +86,14 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
         const bool valid = gid < maxId;
         bool terminate = false, pushShadow = false, splatted = false;
         int matQ = -1;
+        uint32_t seed = 0u;
 
         if (valid)
         {
             const float4 thr = st.thr[gid], r0 = st.ray0[gid], r1 = st.ray1[gid];
             const float4 h0 = st.hit0[gid], h1 = st.hit1[gid], h2 = st.hit2[gid], acc = st.acc[gid];
             f3 T = mk3(thr);
-            uint32_t seed = __float_as_uint(thr.w);
+            seed = __float_as_uint(thr.w);
             const uint32_t len = __float_as_uint(r1.w);
             const f3 rayOrig = mk3(r0), rayDir = mk3(r1);
             const float lastPdfW = r0.w;
@@ -239,8 +248,11 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
                 }
                 matQ = materialQueueOf(mtype, separate);
             }
-            st.thr[gid] = mk4u(T, seed);
-            st.acc[gid] = mk4u(Ei, pixIdx);
+            if (!(REGEN && terminate)) // a regenerated path overwrites both below
+            {
+                st.thr[gid] = mk4u(T, seed);
+                st.acc[gid] = mk4u(Ei, pixIdx);
+            }
         }
 
         // ---- warp-aggregated compaction into the raygen / shadow / material queues ----------------
@@ -260,6 +272,7 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
                 if (!separate && q > FLX_Q_DIFFUSE) continue;
                 const unsigned m = __ballot_sync(FULL, q == FLX_Q_SHADOW ? pushShadow : (myQ == q));
                 if (lane == (unsigned)q) mine = m;
+                if (REGEN && q == FLX_Q_RAYGEN && lane == (unsigned)FLX_Q_EXTENSION) mine = m; // restarted paths
             }
             const unsigned mSplat = checkSpp ? __ballot_sync(FULL, splatted) : 0u;
             if (lane == 9u) mine = mSplat;
@@ -270,7 +283,18 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
             const int srcA = myQ >= 0 ? myQ : 0;
             const uint32_t baseA = __shfl_sync(FULL, base, srcA);
             const unsigned maskA = __shfl_sync(FULL, mine, srcA);
-            if (myQ >= 0) (qs.q[0] + (size_t)myQ * N)[baseA + (uint32_t)__popc(maskA & lt)] = gid; // queues are contiguous, N apart
+            const uint32_t slotA = baseA + (uint32_t)__popc(maskA & lt);
+            if (REGEN)
+            {
+                const uint32_t baseE = __shfl_sync(FULL, base, FLX_Q_EXTENSION);
+                if (myQ == FLX_Q_RAYGEN)
+                {
+                    generateCameraPath(st, gid, seed, *currPixelIdx, slotA, tileRank, tileWorld, params);
+                    qs.q[FLX_Q_EXTENSION][baseE + (uint32_t)__popc(maskA & lt)] = gid;
+                }
+                else if (myQ >= 0) (qs.q[0] + (size_t)myQ * N)[slotA] = gid;
+            }
+            else if (myQ >= 0) (qs.q[0] + (size_t)myQ * N)[slotA] = gid; // queues are contiguous, N apart
             const uint32_t baseS = __shfl_sync(FULL, base, FLX_Q_SHADOW);
             const unsigned maskS = __shfl_sync(FULL, mine, FLX_Q_SHADOW);
             if (pushShadow) qs.q[FLX_Q_SHADOW][baseS + (uint32_t)__popc(maskS & lt)] = gid;
@@ -338,8 +362,17 @@ static inline int wfGrid(const flx_ctx *ctx, uint64_t items)
 
 int flx_launch_logic(flx_ctx *ctx, int firstIteration)
 {
-    k_logic<<<wfGrid(ctx, ctx->N), FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->fb, ctx->mats, ctx->env, ctx->N,
-                                                                     (uint32_t)(firstIteration != 0), ctx->denoiserAOV, ctx->params);
+    k_logic<false><<<wfGrid(ctx, ctx->N), FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->fb, ctx->mats, ctx->env, ctx->N,
+        (uint32_t)(firstIteration != 0), ctx->denoiserAOV, ctx->dPixelIdx, ctx->tileRank, ctx->tileWorld, ctx->params);
+    FLX_LAUNCHED(ctx);
+    return FLX_OK;
+}
+
+// logic + raygen in one launch (the render entry's inner loop; the per-stage API keeps them apart)
+int flx_launch_logic_regen(flx_ctx *ctx)
+{
+    k_logic<true><<<wfGrid(ctx, ctx->N), FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->fb, ctx->mats, ctx->env, ctx->N,
+        0u, ctx->denoiserAOV, ctx->dPixelIdx, ctx->tileRank, ctx->tileWorld, ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
