@@ -80,6 +80,7 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
     const uint32_t rounded = (maxId + 31u) & ~31u;
     const bool checkSpp = params.maxSpp > 0u; // -DCHECK_SPP
     const bool separate = params.wfSeparateQueues != 0u;
+    const uint32_t cursor = REGEN ? *currPixelIdx : 0u;
 
     for (uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x; gid < rounded; gid += gridDim.x * blockDim.x)
     {
@@ -92,6 +93,17 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
         {
             const float4 thr = st.thr[gid], r0 = st.ray0[gid], r1 = st.ray1[gid];
             const float4 h0 = st.hit0[gid], h1 = st.hit1[gid], h2 = st.hit2[gid], acc = st.acc[gid];
+            // the scalar streams and the pending NEE sample are requested together with the rest of the state, so
+            // that the whole record costs one trip to HBM instead of one per use further down
+            const uint32_t shadowBlocked = st.shadowBlocked[gid], lastSpecular = st.lastSpecular[gid];
+            const float lastPickProb = st.lastPickProb[gid];
+            f3 neeContrib = mk3(0.0f);
+            if (shadowBlocked == 0u) // the NEE sample whose shadow ray came back unoccluded (:150-168)
+            {
+                const float4 n0 = st.nee0[gid], n1 = st.nee1[gid], n2 = st.nee2[gid];
+                const float cosTh = st.shw1[gid].w;
+                neeContrib = mk3(n1) * mk3(n2) * mk3(n0) * cosTh / (lastPickProb * n0.w + (float)(params.sampleImpl) * n1.w);
+            }
             f3 T = mk3(thr);
             seed = __float_as_uint(thr.w);
             const uint32_t len = __float_as_uint(r1.w);
@@ -122,9 +134,9 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
                 if (params.useEnvMap)
                 {
                     if (len == 1u || params.sampleImpl) bg = evalEnvMapDir(env, rayDir) * params.envMapStrength;
-                    if (params.sampleImpl && params.sampleExpl && len > 1u && !st.lastSpecular[gid])
+                    if (params.sampleImpl && params.sampleExpl && len > 1u && !lastSpecular)
                     {
-                        const float lightPickProb = st.lastPickProb[gid];
+                        const float lightPickProb = lastPickProb;
                         const float directPdfW = envMapPdf(env, rayDir);
                         weight = (lastPdfW * lightPickProb) / (lastPdfW * lightPickProb + directPdfW);
                     }
@@ -135,26 +147,18 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
             else if (params.useAreaLight && areaLightHit && !terminate) // implicit area-light hit (:126-146)
             {
                 float misWeight = 1.0f;
-                if (params.sampleExpl && len > 1u && !st.lastSpecular[gid])
+                if (params.sampleExpl && len > 1u && !lastSpecular)
                 {
                     const float directPdfA = recip(4.0f * params.areaLight.size.x * params.areaLight.size.y);
                     const float directPdfW = pdfAtoW(directPdfA, length(hitP - rayOrig), -dot(rayDir, hitN));
-                    const float lightPickProb = st.lastPickProb[gid];
+                    const float lightPickProb = lastPickProb;
                     misWeight = lastPdfW / (lastPdfW + directPdfW * lightPickProb);
                 }
                 Ei = Ei + T * misWeight * ld3(params.areaLight.E);
                 terminate = true;
             }
 
-            // resolve the NEE sample whose shadow ray came back unoccluded (:150-168)
-            if (st.shadowBlocked[gid] == 0u)
-            {
-                const float4 n0 = st.nee0[gid], n1 = st.nee1[gid], n2 = st.nee2[gid];
-                const float cosTh = st.shw1[gid].w;
-                const float lightPickProb = st.lastPickProb[gid];
-                const f3 contrib = mk3(n1) * mk3(n2) * mk3(n0) * cosTh / (lightPickProb * n0.w + (float)(params.sampleImpl) * n1.w);
-                Ei = Ei + contrib;
-            }
+            if (shadowBlocked == 0u) Ei = Ei + neeContrib; // resolved after the implicit terms, as the reference orders it
 
             if (terminate) // splat and hand the slot back to raygen (:171-205)
             {
@@ -289,7 +293,7 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
                 const uint32_t baseE = __shfl_sync(FULL, base, FLX_Q_EXTENSION);
                 if (myQ == FLX_Q_RAYGEN)
                 {
-                    generateCameraPath(st, gid, seed, *currPixelIdx, slotA, tileRank, tileWorld, params);
+                    generateCameraPath(st, gid, seed, cursor, slotA, tileRank, tileWorld, params);
                     qs.q[FLX_Q_EXTENSION][baseE + (uint32_t)__popc(maskA & lt)] = gid;
                 }
                 else if (myQ >= 0) (qs.q[0] + (size_t)myQ * N)[slotA] = gid;
@@ -303,7 +307,50 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
 }
 
 // Shared body of the material stages (wf_mat_diffuse.cl:7-66 and its five siblings, wf_mat_all.cl).
-// TYPES is the compile-time set of BxDFs this instantiation can meet in its queue.
+// TYPES is the compile-time set of BxDFs this instantiation can meet in its queue.  Called by whole warps:
+// lane `k` of the queue (k may run past qlen in the last warp), then one aggregated push of the survivors.
+template <int TYPES>
+FLX_DEV void materialBody(const PathState &st, const uint32_t *__restrict__ queue, uint32_t qlen, uint32_t k,
+                          uint32_t *__restrict__ extQueue, uint32_t *extCounter, const MaterialsDev &md)
+{
+    const bool valid = k < qlen;
+    uint32_t gid = 0;
+    if (valid)
+    {
+        gid = queue[k];
+        const float4 thr = st.thr[gid], r1 = st.ray1[gid], h0 = st.hit0[gid], h1 = st.hit1[gid], h2 = st.hit2[gid];
+        uint32_t seed = __float_as_uint(thr.w);
+        SurfHit hit; hit.N = mk3(h1); hit.uvx = h2.x; hit.uvy = h2.y;
+        const Mat mat = loadMat(md.materials + __float_as_int(h2.z));
+        const bool backface = (st.logicFlags[gid] & 1u) != 0u;
+        const f3 dirIn = mk3(r1);
+        const f3 L = mk3(st.shw1[gid]);
+
+        const f3 bsdfNEE = bxdfEval<TYPES>(hit, mat, backface, md, dirIn, L);
+        const float bsdfPdfW = fmaxf(0.0f, bxdfPdf<TYPES>(hit, mat, backface, md, dirIn, L));
+
+        float pdfW = 0.0f;     // the reference leaves these unset for emissive / rejected glossy
+        f3 newDir = mk3(0.0f); // samples; the oracle pins them to 0 and so do we
+        const f3 bsdf = bxdfSample<TYPES>(hit, mat, backface, md, dirIn, newDir, pdfW, seed);
+
+        const f3 oldT = mk3(thr);
+        f3 newT;
+        if (pdfW == 0.0f || isZero(bsdf)) newT = mk3(0.0f);
+        else newT = oldT * bsdf * dot(hit.N, newDir) / pdfW;
+        const f3 orig = mk3(h0) + 1e-4f * newDir;
+
+        st.nee1[gid] = mk4(bsdfNEE, bsdfPdfW);
+        st.nee2[gid] = mk4(oldT, 0.0f);
+        st.thr[gid] = mk4u(newT, seed);
+        st.ray0[gid] = mk4(orig, pdfW);
+        st.ray1[gid] = make_float4(newDir.x, newDir.y, newDir.z, r1.w);
+        st.lastSpecular[gid] = FLX_BXDF_IS_SINGULAR(mat.type) ? 1u : 0u;
+    }
+    const uint32_t slot = warpPush(extCounter, valid);
+    if (valid) extQueue[slot] = gid;
+}
+
+// one queue, one launch: wf_mat_all.cl (no separate queues) and the building block of the tests
 template <int TYPES>
 __global__ void __launch_bounds__(FLX_WF_THREADS, FLX_MAT_MIN_BLOCKS)
 k_material(PathState st, const uint32_t *__restrict__ queue, const uint32_t *__restrict__ queueLen,
@@ -312,42 +359,42 @@ k_material(PathState st, const uint32_t *__restrict__ queue, const uint32_t *__r
     const uint32_t qlen = *queueLen;
     const uint32_t rounded = (qlen + 31u) & ~31u;
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < rounded; k += gridDim.x * blockDim.x)
+        materialBody<TYPES>(st, queue, qlen, k, extQueue, extCounter, md);
+}
+
+// The six material queues of CLContext::enqueueWfMaterialKernels (clcontext.cpp:816-831) in ONE launch: the
+// queues are laid end to end in units of 32-path chunks and every warp takes chunks round robin, running the
+// specialised body of the queue its chunk belongs to.  Most queues are short (a few thousand paths), so six
+// launches spend their time ramping up and draining; together they fill the machine once.
+__global__ void __launch_bounds__(FLX_WF_THREADS, FLX_MAT_MIN_BLOCKS)
+k_materials_separate(PathState st, Queues qs, uint32_t N, MaterialsDev md)
+{
+    const uint32_t *cnt = (const uint32_t *)qs.counters; // word q = length of queue q
+    uint32_t end[6];                                      // chunk index one past queue FLX_Q_DIFFUSE + i
+    uint32_t acc = 0u;
+#pragma unroll
+    for (int i = 0; i < 6; i++) { acc += (cnt[FLX_Q_DIFFUSE + i] + 31u) >> 5; end[i] = acc; }
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warpsTotal = (gridDim.x * blockDim.x) >> 5;
+    uint32_t *extQueue = qs.q[FLX_Q_EXTENSION], *extCounter = &qs.counters->extensionQueue;
+    for (uint32_t chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; chunk < acc; chunk += warpsTotal)
     {
-        const bool valid = k < qlen;
-        uint32_t gid = 0;
-        if (valid)
+        int i = 0;
+        uint32_t first = 0u;
+#pragma unroll
+        for (int j = 0; j < 5; j++) if (chunk >= end[j]) { i = j + 1; first = end[j]; }
+        const uint32_t k = ((chunk - first) << 5) + lane;
+        const uint32_t *queue = qs.q[0] + (size_t)(FLX_Q_DIFFUSE + i) * N; // queues are contiguous, N apart
+        const uint32_t qlen = cnt[FLX_Q_DIFFUSE + i];
+        switch (i) // warp-uniform
         {
-            gid = queue[k];
-            const float4 thr = st.thr[gid], r1 = st.ray1[gid], h0 = st.hit0[gid], h1 = st.hit1[gid], h2 = st.hit2[gid];
-            uint32_t seed = __float_as_uint(thr.w);
-            SurfHit hit; hit.N = mk3(h1); hit.uvx = h2.x; hit.uvy = h2.y;
-            const Mat mat = loadMat(md.materials + __float_as_int(h2.z));
-            const bool backface = (st.logicFlags[gid] & 1u) != 0u;
-            const f3 dirIn = mk3(r1);
-            const f3 L = mk3(st.shw1[gid]);
-
-            const f3 bsdfNEE = bxdfEval<TYPES>(hit, mat, backface, md, dirIn, L);
-            const float bsdfPdfW = fmaxf(0.0f, bxdfPdf<TYPES>(hit, mat, backface, md, dirIn, L));
-            st.nee1[gid] = mk4(bsdfNEE, bsdfPdfW);
-
-            float pdfW = 0.0f;     // the reference leaves these unset for emissive / rejected glossy
-            f3 newDir = mk3(0.0f); // samples; the oracle pins them to 0 and so do we
-            const f3 bsdf = bxdfSample<TYPES>(hit, mat, backface, md, dirIn, newDir, pdfW, seed);
-
-            const f3 oldT = mk3(thr);
-            f3 newT;
-            if (pdfW == 0.0f || isZero(bsdf)) newT = mk3(0.0f);
-            else newT = oldT * bsdf * dot(hit.N, newDir) / pdfW;
-            const f3 orig = mk3(h0) + 1e-4f * newDir;
-
-            st.nee2[gid] = mk4(oldT, 0.0f);
-            st.thr[gid] = mk4u(newT, seed);
-            st.ray0[gid] = mk4(orig, pdfW);
-            st.ray1[gid] = make_float4(newDir.x, newDir.y, newDir.z, r1.w);
-            st.lastSpecular[gid] = FLX_BXDF_IS_SINGULAR(mat.type) ? 1u : 0u;
+        case 0: materialBody<FLX_BXDF_DIFFUSE>(st, queue, qlen, k, extQueue, extCounter, md); break;
+        case 1: materialBody<FLX_BXDF_GLOSSY>(st, queue, qlen, k, extQueue, extCounter, md); break;
+        case 2: materialBody<FLX_BXDF_GGX_ROUGH_REFLECTION>(st, queue, qlen, k, extQueue, extCounter, md); break;
+        case 3: materialBody<FLX_BXDF_GGX_ROUGH_DIELECTRIC>(st, queue, qlen, k, extQueue, extCounter, md); break;
+        case 4: materialBody<FLX_BXDF_IDEAL_REFLECTION | FLX_BXDF_IDEAL_DIELECTRIC>(st, queue, qlen, k, extQueue, extCounter, md); break;
+        default: materialBody<FLX_BXDF_EMISSIVE>(st, queue, qlen, k, extQueue, extCounter, md); break;
         }
-        const uint32_t slot = warpPush(extCounter, valid);
-        if (valid) extQueue[slot] = gid;
     }
 }
 
@@ -390,17 +437,9 @@ int flx_launch_materials(flx_ctx *ctx)
         FLX_LAUNCHED(ctx);
         return FLX_OK;
     }
-    k_material<FLX_BXDF_DIFFUSE><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_DIFFUSE], counterOf(ctx->qs.counters, FLX_Q_DIFFUSE), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
-    FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_GLOSSY><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_GLOSSY], counterOf(ctx->qs.counters, FLX_Q_GLOSSY), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
-    FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_GGX_ROUGH_REFLECTION><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_GGX_REFL], counterOf(ctx->qs.counters, FLX_Q_GGX_REFL), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
-    FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_GGX_ROUGH_DIELECTRIC><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_GGX_REFR], counterOf(ctx->qs.counters, FLX_Q_GGX_REFR), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
-    FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_IDEAL_REFLECTION | FLX_BXDF_IDEAL_DIELECTRIC><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_DELTA], counterOf(ctx->qs.counters, FLX_Q_DELTA), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
-    FLX_LAUNCHED(ctx);
-    k_material<FLX_BXDF_EMISSIVE><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_EMISSIVE], counterOf(ctx->qs.counters, FLX_Q_EMISSIVE), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
+    static_assert(FLX_Q_GLOSSY == FLX_Q_DIFFUSE + 1 && FLX_Q_GGX_REFL == FLX_Q_DIFFUSE + 2 && FLX_Q_GGX_REFR == FLX_Q_DIFFUSE + 3 &&
+                  FLX_Q_DELTA == FLX_Q_DIFFUSE + 4 && FLX_Q_EMISSIVE == FLX_Q_DIFFUSE + 5, "material queues are consecutive");
+    k_materials_separate<<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->N, ctx->mats);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
