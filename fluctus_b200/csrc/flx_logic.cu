@@ -9,7 +9,7 @@
 #define FLX_LOGIC_MIN_BLOCKS 4
 #endif
 #ifndef FLX_MAT_MIN_BLOCKS
-#define FLX_MAT_MIN_BLOCKS 1
+#define FLX_MAT_MIN_BLOCKS 4
 #endif
 
 FLX_DEV uint32_t warpPush(uint32_t *counter, bool pred) // see flx_wavefront.cu
