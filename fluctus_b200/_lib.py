@@ -38,6 +38,14 @@ SIGNATURES = {
     "flx_postprocess": (I32, [V]),
     "flx_finish": (I32, [V]),
     "flx_render": (I32, [V, U32, I32]),
+    "flx_mk_reset": (I32, [V]),
+    "flx_mk_raygen": (I32, [V]),
+    "flx_mk_next_vertex": (I32, [V]),
+    "flx_mk_sample_bsdf": (I32, [V]),
+    "flx_mk_splat": (I32, [V]),
+    "flx_mk_splat_preview": (I32, [V]),
+    "flx_mk_get_stats": (I32, [V, V]),
+    "flx_mk_render": (I32, [V, U32, I32]),
     "flx_get_render_totals": (I32, [V, V]),
     "flx_read_pixels": (I32, [V, I32, V, SZ]),
     "flx_write_pixels": (I32, [V, I32, V, SZ]),

@@ -131,6 +131,24 @@ class CudaContext:
         self._check(self.L.flx_get_render_totals(self.h, _p(t)))
         return dict(zip(("primary", "extension", "shadow", "samples", "splatted", "iterations"), (int(x) for x in t)))
 
+    # ---- microkernel renderer (clcontext.cpp:727-768 -> src/mk_*.cl): one task per pixel, exact spp
+    def enqueueResetKernel(self, params=None): self._check(self.L.flx_mk_reset(self.h))
+    def enqueueRayGenKernel(self, params=None): self._check(self.L.flx_mk_raygen(self.h))
+    def enqueueNextVertexKernel(self, params=None): self._check(self.L.flx_mk_next_vertex(self.h))
+    def enqueueBsdfSampleKernel(self, params=None): self._check(self.L.flx_mk_sample_bsdf(self.h))
+    def enqueueSplatKernel(self, params=None): self._check(self.L.flx_mk_splat(self.h))
+    def enqueueSplatPreviewKernel(self, params=None): self._check(self.L.flx_mk_splat_preview(self.h))
+
+    def renderSingle(self, spp, reset=True):
+        """Tracer::renderSingle's loop (tracer.cpp:130-159) replayed from a CUDA graph: exactly `spp` samples per pixel."""
+        self._check(self.L.flx_mk_render(self.h, int(spp), int(bool(reset))))
+
+    def getStats(self):
+        """Device RenderStats maintained by the MK kernels (synchronises)."""
+        st = np.zeros(4, np.uint32)
+        self._check(self.L.flx_mk_get_stats(self.h, _p(st)))
+        return dict(zip(("primaryRays", "extensionRays", "shadowRays", "samples"), (int(x) for x in st)))
+
     # ---- results
     def readPixels(self, which=BUF_PIXELS, out=None):
         n = self.width * self.height

@@ -156,6 +156,61 @@ int flx_render(flx_ctx *ctx, uint32_t iterations, int do_reset)
     return FLX_OK;
 }
 
+// ---- microkernel renderer (CLContext::enqueueResetKernel ... enqueueSplatPreviewKernel, clcontext.cpp:727-768) ----
+#define FLX_MK_ENTRY(ctx, needScene) FLX_CHECK_CTX(ctx); FLX_CUDA(ctx, cudaSetDevice((ctx)->device)); FLX_TRY(flx_ready(ctx, needScene))
+int flx_mk_reset(flx_ctx *ctx) { FLX_MK_ENTRY(ctx, false); return flx_launch_mk_reset(ctx); }
+int flx_mk_raygen(flx_ctx *ctx) { FLX_MK_ENTRY(ctx, false); return flx_launch_mk_raygen(ctx); }
+int flx_mk_next_vertex(flx_ctx *ctx) { FLX_MK_ENTRY(ctx, true); return flx_launch_mk_next_vertex(ctx); }
+int flx_mk_sample_bsdf(flx_ctx *ctx) { FLX_MK_ENTRY(ctx, true); return flx_launch_mk_sample_bsdf(ctx); }
+int flx_mk_splat(flx_ctx *ctx) { FLX_MK_ENTRY(ctx, false); return flx_launch_mk_splat(ctx); }
+int flx_mk_splat_preview(flx_ctx *ctx) { FLX_MK_ENTRY(ctx, false); return flx_launch_mk_splat_preview(ctx); }
+
+int flx_mk_get_stats(flx_ctx *ctx, flx_render_stats *out)
+{
+    FLX_CHECK_CTX(ctx); FLX_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!out) return flx_fail(ctx, FLX_ERR_ARG, "flx_mk_get_stats: null output");
+    FLX_CUDA(ctx, cudaMemcpyAsync(out, ctx->dStats, sizeof(*out), cudaMemcpyDeviceToHost, ctx->stream));
+    return flx_finish(ctx);
+}
+
+// Tracer::renderSingle (tracer.cpp:108-182): every pixel gets exactly `spp` more samples
+int flx_mk_render(flx_ctx *ctx, uint32_t spp, int do_reset)
+{
+    FLX_MK_ENTRY(ctx, true);
+    if (ctx->params.maxBounces == 0u) return flx_fail(ctx, FLX_ERR_ARG, "flx_mk_render: maxBounces = 0 (unbounded paths) has no fixed schedule");
+    if (ctx->params.useRoulette) return flx_fail(ctx, FLX_ERR_ARG, "flx_mk_render: switch Russian roulette off first (tracer.cpp:118-122)");
+    if (do_reset) FLX_TRY(flx_launch_mk_reset(ctx));
+    if (spp == 0) return FLX_OK;
+    if (!ctx->mkGraphValid)
+    {
+        cudaGraph_t graph = nullptr;
+        FLX_CUDA(ctx, cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+        const uint64_t before = ctx->launches;
+        int rc = flx_launch_mk_raygen(ctx);
+        for (uint32_t b = 0; rc == FLX_OK && b < ctx->params.maxBounces + 1u; b++)
+        {
+            rc = flx_launch_mk_next_vertex(ctx);
+            if (rc == FLX_OK) rc = flx_launch_mk_sample_bsdf(ctx);
+        }
+        if (rc == FLX_OK) rc = flx_launch_mk_splat(ctx);
+        ctx->mkGraphKernels = ctx->launches - before;
+        ctx->launches = before;
+        cudaError_t e = cudaStreamEndCapture(ctx->stream, &graph);
+        if (rc != FLX_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (e != cudaSuccess) return flx_fail(ctx, FLX_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
+        e = cudaGraphInstantiate(&ctx->mkGraphExec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) return flx_fail(ctx, FLX_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+        ctx->mkGraphValid = true;
+    }
+    for (uint32_t s = 0; s < spp; s++)
+    {
+        FLX_CUDA(ctx, cudaGraphLaunch(ctx->mkGraphExec, ctx->stream));
+        ctx->launches += ctx->mkGraphKernels;
+    }
+    return FLX_OK;
+}
+
 int flx_get_render_totals(flx_ctx *ctx, uint64_t totals[6])
 {
     FLX_CHECK_CTX(ctx); FLX_CUDA(ctx, cudaSetDevice(ctx->device));

@@ -305,3 +305,26 @@ FLX_DEV float bxdfPdf(const SurfHit &h, const Mat &m, bool backface, const Mater
     if (FLX_HAS(FLX_BXDF_GGX_ROUGH_DIELECTRIC) && t == FLX_BXDF_GGX_ROUGH_DIELECTRIC) return pdfGGXRefract(h, m, backface, dirIn, dirOut);
     return 0.0f;
 }
+
+// utils.cl:174-207 — only reached for materials with a normal map
+FLX_DEV f3 tangentSpaceNormal(f3 hitN, float uvx, float uvy, int hitI, int mapN, const MaterialsDev &md)
+{
+    f3 texNormal = readTexture(uvx, uvy, md.textures[mapN], md.texels);
+    texNormal = texNormal + texNormal - mk3(1.0f, 1.0f, 1.0f);
+    const flx_triangle *t = md.tris160 + hitI;
+    const f3 e1 = ld3(t->v1.p) - ld3(t->v0.p);
+    const f3 e2 = ld3(t->v2.p) - ld3(t->v0.p);
+    const f3 t1 = ld3(t->v1.t) - ld3(t->v0.t);
+    const f3 t2 = ld3(t->v2.t) - ld3(t->v0.t);
+    const float det = (t1.x * t2.y - t1.y * t2.x);
+    if (det == 0.0f) return hitN;
+    const float invDet = recip(det);
+    const f3 T = normalize(invDet * (e1 * t2.y - e2 * t1.y));
+    const f3 B = normalize(invDet * (e2 * t1.x - e1 * t2.x));
+    f3 N;
+    N.x = T.x * texNormal.x + B.x * texNormal.y + hitN.x * texNormal.z;
+    N.y = T.y * texNormal.x + B.y * texNormal.y + hitN.y * texNormal.z;
+    N.z = T.z * texNormal.x + B.z * texNormal.y + hitN.z * texNormal.z;
+    return normalize(N);
+}
+

@@ -20,6 +20,8 @@ static void invalidateGraph(flx_ctx *ctx)
 {
     if (ctx->graphExec) { cudaGraphExecDestroy(ctx->graphExec); ctx->graphExec = nullptr; }
     ctx->graphValid = false;
+    if (ctx->mkGraphExec) { cudaGraphExecDestroy(ctx->mkGraphExec); ctx->mkGraphExec = nullptr; }
+    ctx->mkGraphValid = false;
 }
 
 // ---- stage timers ---------------------------------------------------------------------------------
@@ -68,7 +70,7 @@ int flx_create(flx_ctx **out, int device, uint32_t num_tasks, void *cuda_stream)
     if (cuda_stream) ctx->stream = (cudaStream_t)cuda_stream;
     else { CREATE_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->ownStream = true; }
 
-    // path state: twelve float4 streams + four scalar streams, zero-initialised like a fresh cl::Buffer
+    // path state: twelve float4 streams + five scalar streams, zero-initialised like a fresh cl::Buffer
     // is not — the oracle starts from zeros too, so untouched fields compare equal.
     const size_t N = num_tasks;
     const size_t stateBytes = N * (FLX_STATE_VEC_STREAMS * sizeof(float4) + FLX_STATE_SCALAR_STREAMS * 4);
@@ -81,6 +83,7 @@ int flx_create(flx_ctx **out, int device, uint32_t num_tasks, void *cuda_stream)
         for (int i = 0; i < FLX_STATE_VEC_STREAMS; i++) *dst[i] = v + (size_t)i * N;
         uint32_t *s = (uint32_t *)(v + (size_t)FLX_STATE_VEC_STREAMS * N);
         ctx->st.lastSpecular = s; ctx->st.shadowBlocked = s + N; ctx->st.logicFlags = s + 2 * N; ctx->st.lastPickProb = (float *)(s + 3 * N);
+        ctx->st.phase = (int32_t *)(s + 4 * N);
     }
     // queues + counters + cursors + totals
     const size_t queueBytes = FLX_NUM_QUEUES * N * 4 + 512;
@@ -93,6 +96,7 @@ int flx_create(flx_ctx **out, int device, uint32_t num_tasks, void *cuda_stream)
         ctx->qs.counters = (flx_queue_counters *)tail;       // 40 B
         ctx->dPixelIdx = (uint32_t *)(tail + 64);            // pixel cursor + 2 work cursors
         ctx->dTotals = (RenderTotals *)(tail + 128);         // 48 B
+        ctx->dStats = (flx_render_stats *)(tail + 192);      // 16 B
         ctx->dTraceStats = (unsigned long long *)(tail + 256); // 20 x u64
     }
     CREATE_CUDA(cudaMallocHost(&ctx->hCounters, 64 * sizeof(flx_queue_counters)));

@@ -32,9 +32,13 @@ struct PathState
     float4 *ray0, *ray1, *hit0, *hit1, *hit2, *thr, *acc, *shw0, *shw1, *nee0, *nee1, *nee2;
     uint32_t *lastSpecular, *shadowBlocked, *logicFlags;
     float *lastPickProb;
+    int32_t *phase; // microkernel renderer only (PathPhase, geom.h:205-216)
 };
+// PathPhase (geom.h:205-216) and the values the microkernel stages park in shadowBlocked while a shadow ray is out
+enum { FLX_MK_RT_NEXT_VERTEX = 0, FLX_MK_SAMPLE_BSDF = 1, FLX_MK_SPLAT_SAMPLE = 4, FLX_MK_GENERATE_CAMERA_RAY = 5, FLX_MK_DONE = 6 };
+enum { FLX_MK_NEE_PENDING = 2u, FLX_MK_NEE_NONE = 3u };
 #define FLX_STATE_VEC_STREAMS 12
-#define FLX_STATE_SCALAR_STREAMS 4
+#define FLX_STATE_SCALAR_STREAMS 5
 
 struct Queues
 {
@@ -100,6 +104,7 @@ struct flx_ctx
     void *queueBlock = nullptr; Queues qs{};
     uint32_t *dPixelIdx = nullptr;
     RenderTotals *dTotals = nullptr;
+    flx_render_stats *dStats = nullptr; // device RenderStats of the microkernel renderer
     FrameBuffers fb{}; void *fbBlock = nullptr;
     flx_render_params params{}; bool paramsSet = false;
     int denoiserAOV = 0; uint32_t seedOffset = 0;
@@ -109,6 +114,8 @@ struct flx_ctx
 
     // graph for flx_render
     cudaGraphExec_t graphExec = nullptr; bool graphValid = false; uint64_t graphKernels = 0;
+    // graph for flx_mk_render: one sample per pixel (raygen, (nextVertex, sampleBsdf) x (maxBounces + 1), splat)
+    cudaGraphExec_t mkGraphExec = nullptr; bool mkGraphValid = false; uint64_t mkGraphKernels = 0;
 
     // timing
     bool timing = false; StageTimer timers[6];
@@ -139,6 +146,17 @@ int flx_launch_ext(flx_ctx *ctx);
 int flx_launch_shadow(flx_ctx *ctx);
 int flx_launch_trace_batch(flx_ctx *ctx, const float4 *dRays, size_t n, int32_t *dHitI, float *dHitT, flx_hit *dHits);
 int flx_launch_any_batch(flx_ctx *ctx, const float4 *dRays, size_t n, uint8_t *dOcc);
+
+int flx_launch_mk_vertex_trace(flx_ctx *ctx, uint32_t total);
+int flx_launch_mk_shadow_trace(flx_ctx *ctx, uint32_t total, int lightOccludes);
+
+// implemented in flx_microkernel.cu (src/mk_*.cl)
+int flx_launch_mk_reset(flx_ctx *ctx);
+int flx_launch_mk_raygen(flx_ctx *ctx);
+int flx_launch_mk_next_vertex(flx_ctx *ctx);
+int flx_launch_mk_sample_bsdf(flx_ctx *ctx);
+int flx_launch_mk_splat(flx_ctx *ctx);
+int flx_launch_mk_splat_preview(flx_ctx *ctx);
 
 // implemented in flx_wavefront.cu
 int flx_launch_reset(flx_ctx *ctx);

@@ -19,20 +19,10 @@ FLX_DEV void resetPathFields(const PathState &st, uint32_t gid, float worldRadiu
     st.lastPickProb[gid] = 1.0f;
 }
 
-// Path `gid` restarts at the pixel that raygen-queue position `k` maps to (wf_raygen.cl:25: (cursor + k) %
-// numPixels), with the RNG state `seed` the terminated path left behind.
-FLX_DEV void generateCameraPath(const PathState &st, uint32_t gid, uint32_t seed, uint32_t cursor, uint32_t k,
-                                uint32_t tileRank, uint32_t tileWorld, const flx_render_params &params)
+// Jittered pinhole / thin-lens camera ray through pixel `pixelIdx` (wf_raygen.cl:27-70 == mk_raygen.cl:20-58)
+FLX_DEV void cameraRay(uint32_t pixelIdx, uint32_t &seed, const flx_render_params &params, f3 &rayOrig, f3 &rayDirection)
 {
     const flx_camera &cam = params.camera;
-    uint32_t pixelIdx = (cursor + k) % (params.width * params.height);
-    if (tileWorld > 1u) // preview sharding: this rank owns the image rows y % tileWorld == tileRank
-    {
-        const uint32_t ownedRows = (params.height - tileRank + tileWorld - 1u) / tileWorld;
-        const uint32_t j = (cursor + k) % (ownedRows * params.width);
-        pixelIdx = ((j / params.width) * tileWorld + tileRank) * params.width + (j % params.width);
-    }
-
     float x = (float)(pixelIdx % params.width);
     float y = (float)(pixelIdx) * params.width1; // deliberately not floored, as the reference
     x += rnd(seed);
@@ -45,9 +35,9 @@ FLX_DEV void generateCameraPath(const PathState &st, uint32_t gid, uint32_t seed
     SCRx *= cam.fovSCALE;
     SCRy *= cam.fovSCALE;
 
-    f3 rayOrig = ld3(cam.pos);
+    rayOrig = ld3(cam.pos);
     const f3 rayTarget = rayOrig + ld3(cam.right) * SCRx + ld3(cam.up) * SCRy + ld3(cam.dir);
-    f3 rayDirection = normalize(rayTarget - rayOrig);
+    rayDirection = normalize(rayTarget - rayOrig);
     if (cam.apertureSize > 0.0f) // thin lens
     {
         const f3 fp = ld3(cam.pos) + rayDirection * cam.focalDist;
@@ -56,6 +46,22 @@ FLX_DEV void generateCameraPath(const PathState &st, uint32_t gid, uint32_t seed
         rayOrig += params.worldRadius * cam.apertureSize * (ld3(cam.right) * dx + ld3(cam.up) * dy);
         rayDirection = normalize(fp - rayOrig);
     }
+}
+
+// Path `gid` restarts at the pixel that raygen-queue position `k` maps to (wf_raygen.cl:25: (cursor + k) %
+// numPixels), with the RNG state `seed` the terminated path left behind.
+FLX_DEV void generateCameraPath(const PathState &st, uint32_t gid, uint32_t seed, uint32_t cursor, uint32_t k,
+                                uint32_t tileRank, uint32_t tileWorld, const flx_render_params &params)
+{
+    uint32_t pixelIdx = (cursor + k) % (params.width * params.height);
+    if (tileWorld > 1u) // preview sharding: this rank owns the image rows y % tileWorld == tileRank
+    {
+        const uint32_t ownedRows = (params.height - tileRank + tileWorld - 1u) / tileWorld;
+        const uint32_t j = (cursor + k) % (ownedRows * params.width);
+        pixelIdx = ((j / params.width) * tileWorld + tileRank) * params.width + (j % params.width);
+    }
+    f3 rayOrig, rayDirection;
+    cameraRay(pixelIdx, seed, params, rayOrig, rayDirection);
     st.ray0[gid] = mk4(rayOrig, 1.0f);                   // orig, lastPdfW = 1
     st.ray1[gid] = mk4u(rayDirection, 0u);               // dir, pathLen = 0
     st.thr[gid] = mk4u(mk3(1.0f), seed);                 // T = 1, seed

@@ -100,6 +100,45 @@ struct ShadowJob
     }
 };
 
+// Microkernel renderer (src/mk_next_vertex.cl:33-41): the closest-hit part of `nextVertex` for every task in phase
+// MK_RT_NEXT_VERTEX.  No queue: task k is pixel k, tasks in other phases are skipped at load time.  The result
+// handling is ExtJob's (hit record + pathLen); the shading half of the stage runs in k_mk_vertex_shade.
+struct MkVertexJob
+{
+    ExtJob ext;
+    FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
+    {
+        if (ext.st.phase[k] != FLX_MK_RT_NEXT_VERTEX) return false;
+        ext.gid = k;
+        o = mk3(ext.st.ray0[k]); d = mk3(ext.st.ray1[k]); tmax = FLX_FLT_MAX;
+        return true;
+    }
+    FLX_DEV void store(const RayHit &h, f3 o, f3 d) { ext.store(h, o, d); }
+};
+
+// The inline shadow rays of src/mk_sample_bsdf.cl:90-96 (environment sample: the light quad occludes too, LIGHT =
+// true) and :121-126 (area-light sample: hierarchy only).  A task takes part when its NEE slot says "pending".
+template <bool LIGHT>
+struct MkShadowJob
+{
+    const PathState &st; const flx_render_params &params;
+    uint32_t gid;
+    FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
+    {
+        if (st.shadowBlocked[k] != FLX_MK_NEE_PENDING) return false;
+        gid = k;
+        const float4 s0 = st.shw0[k];
+        o = mk3(s0); d = mk3(st.shw1[k]); tmax = s0.w;
+        if (LIGHT && params.useAreaLight)
+        {
+            float t = tmax;
+            if (intersectLight(makeLightGeom(params.areaLight), o, d, t)) { st.shadowBlocked[k] = 1u; return false; }
+        }
+        return true;
+    }
+    FLX_DEV void store(const RayHit &h, f3, f3) { st.shadowBlocked[gid] = h.slot >= 0 ? 1u : 0u; }
+};
+
 // ray batch, closest hit: rays as 2 x float4 {o.xyz, tmax} {d.xyz, -}
 struct BatchJob
 {
@@ -184,6 +223,27 @@ k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
+__global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
+k_mk_vertex(DevBVH bvh, PathState st, unsigned int total, unsigned int *cursor, const __grid_constant__ flx_render_params params)
+{
+    extern __shared__ float4 topNodes[];
+    stageTopNodes(bvh, topNodes);
+    MkVertexJob job = {{bvh, st, nullptr, params, 0u, 0u, 0u}};
+    TravCount cnt = {0u, 0u, 0u};
+    traceLoop<false, false>(bvh, topNodes, job, cursor, total, cnt);
+}
+
+template <bool LIGHT>
+__global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
+k_mk_shadow(DevBVH bvh, PathState st, unsigned int total, unsigned int *cursor, const __grid_constant__ flx_render_params params)
+{
+    extern __shared__ float4 topNodes[];
+    stageTopNodes(bvh, topNodes);
+    MkShadowJob<LIGHT> job = {st, params, 0u};
+    TravCount cnt = {0u, 0u, 0u};
+    traceLoop<true, false>(bvh, topNodes, job, cursor, total, cnt);
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
@@ -221,7 +281,8 @@ static cudaError_t traceKernelSetup(flx_ctx *ctx)
 {
     if (ctx->traceSetupDone) return cudaSuccess;
     const void *kernels[] = {(const void *)k_ext<false>, (const void *)k_ext<true>, (const void *)k_shadow<false>, (const void *)k_shadow<true>,
-                             (const void *)k_trace_batch<false>, (const void *)k_trace_batch<true>, (const void *)k_any_batch<false>, (const void *)k_any_batch<true>};
+                             (const void *)k_trace_batch<false>, (const void *)k_trace_batch<true>, (const void *)k_any_batch<false>, (const void *)k_any_batch<true>,
+                             (const void *)k_mk_vertex, (const void *)k_mk_shadow<false>, (const void *)k_mk_shadow<true>};
     for (const void *k : kernels)
     {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FLX_TOP_SMEM_BYTES);
@@ -245,6 +306,28 @@ int flx_launch_ext(flx_ctx *ctx)
         k_ext<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, ctx->dTraceStats, ctx->params);
     else
         k_ext<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, nullptr, ctx->params);
+    FLX_LAUNCHED(ctx);
+    return FLX_OK;
+}
+
+// microkernel renderer: traversal halves of nextVertex / sampleBsdf over tasks [0, total)
+int flx_launch_mk_vertex_trace(flx_ctx *ctx, uint32_t total)
+{
+    FLX_CUDA(ctx, traceKernelSetup(ctx));
+    unsigned int *cur = workCursor(ctx, 0);
+    FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
+    k_mk_vertex<<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, total, cur, ctx->params);
+    FLX_LAUNCHED(ctx);
+    return FLX_OK;
+}
+
+int flx_launch_mk_shadow_trace(flx_ctx *ctx, uint32_t total, int lightOccludes)
+{
+    FLX_CUDA(ctx, traceKernelSetup(ctx));
+    unsigned int *cur = workCursor(ctx, 1);
+    FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
+    if (lightOccludes) k_mk_shadow<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, total, cur, ctx->params);
+    else k_mk_shadow<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, total, cur, ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }

@@ -158,6 +158,7 @@ __global__ void k_export_state(PathState st, uint32_t *s, uint32_t N)
         const uint32_t lf = st.logicFlags[gid];
         PUTW(FLX_SLOT_BACKFACE, lf & 1u); PUTW(FLX_SLOT_FIRST_DIFFUSE, (lf >> 1) & 1u);
         PUTW(FLX_SLOT_LAST_PICK_PROB, __float_as_uint(st.lastPickProb[gid]));
+        PUTW(FLX_SLOT_PHASE, (uint32_t)st.phase[gid]);
     }
 }
 
@@ -182,6 +183,7 @@ __global__ void k_import_state(PathState st, const uint32_t *s, uint32_t N)
         st.shadowBlocked[gid] = GETW(FLX_SLOT_SHADOW_BLOCKED);
         st.logicFlags[gid] = (GETW(FLX_SLOT_BACKFACE) & 1u) | ((GETW(FLX_SLOT_FIRST_DIFFUSE) & 1u) << 1);
         st.lastPickProb[gid] = __uint_as_float(GETW(FLX_SLOT_LAST_PICK_PROB));
+        st.phase[gid] = (int32_t)GETW(FLX_SLOT_PHASE);
     }
 }
 

@@ -83,6 +83,18 @@ public:
     void enqueueGetCounters(QueueCounters *cnt) { check(flx_get_counters(ctx, cnt)); }
     void finishQueue() { check(flx_finish(ctx)); }
 
+    // ---- microkernel renderer (src/clcontext.cpp:727-768 -> mk_*.cl): one task per pixel, exact spp ---------
+    void enqueueResetKernel(const RenderParams &) { check(flx_mk_reset(ctx)); }
+    void enqueueRayGenKernel(const RenderParams &) { check(flx_mk_raygen(ctx)); }
+    void enqueueNextVertexKernel(const RenderParams &) { check(flx_mk_next_vertex(ctx)); }
+    void enqueueBsdfSampleKernel(const RenderParams &) { check(flx_mk_sample_bsdf(ctx)); }
+    void enqueueSplatKernel(const RenderParams &) { check(flx_mk_splat(ctx)); }
+    void enqueueSplatPreviewKernel(const RenderParams &) { check(flx_mk_splat_preview(ctx)); }
+    // Tracer::renderSingle's loop (src/tracer.cpp:130-159) from a CUDA graph
+    void renderSingle(uint32_t spp, bool reset = true) { check(flx_mk_render(ctx, spp, reset ? 1 : 0)); }
+    // CLContext::fetchStatsAsync (src/clcontext.cpp:660-664): the device RenderStats of the MK kernels
+    void fetchStats() { check(flx_mk_get_stats(ctx, &statsAsync)); }
+
     // ---- headless render entry (new): n passes of the benchmark inner loop from a CUDA graph ---------
     void render(uint32_t iterations, bool reset = false) { check(flx_render(ctx, iterations, reset ? 1 : 0)); }
     struct Totals { uint64_t primary, extension, shadow, samples, splatted, iterations; };

@@ -108,6 +108,21 @@ class Tracer:
                 break
         return c.getRenderTotals()
 
+    # Tracer::renderSingle (tracer.cpp:108-182): final frame with a predefined spp on the microkernel renderer —
+    # the only mode that guarantees the sample count of every pixel; images are deterministic
+    def renderSingle(self, spp):
+        """Exactly `spp` samples per pixel (this rank's share when world_size > 1: spp // world, remainder to low
+        ranks).  Needs num_tasks >= width * height.  Returns the device RenderStats."""
+        c, p = self.clctx, self.params[0]
+        if c.NUM_TASKS < int(p["width"]) * int(p["height"]):
+            raise ValueError("renderSingle: NUM_TASKS must cover the image (mk_raygen.cl:8-9)")
+        if int(p["useRoulette"]):
+            p["useRoulette"] = 0  # "Turning off russian roulette" (tracer.cpp:118-122)
+            c.updateParams(self.params)
+        share = int(spp) // self.world_size + (1 if self.rank < int(spp) % self.world_size else 0)
+        c.renderSingle(share, reset=True)
+        return c.getStats()
+
     def postprocess(self):
         self.clctx.enqueuePostprocessKernel(self.params)
 

@@ -108,6 +108,25 @@ int flx_render(flx_ctx *ctx, uint32_t iterations, int do_reset);
  * shadow, samples, splatted, iterations} (definitions of tracer.cpp:761-765).  Synchronises. */
 int flx_get_render_totals(flx_ctx *ctx, uint64_t totals[6]);
 
+/* ---- microkernel ("MK") renderer: one task per pixel, exact sample counts, deterministic images ------------
+ * CLContext::enqueueResetKernel / RayGenKernel / NextVertexKernel / BsdfSampleKernel / SplatKernel /
+ * SplatPreviewKernel (clcontext.cpp:727-768) -> mk_reset.cl, mk_raygen.cl, mk_next_vertex.cl,
+ * mk_sample_bsdf.cl, mk_splat.cl, mk_splat_preview.cl.  Needs NUM_TASKS >= width * height to cover the
+ * image (tasks beyond min(w*h, NUM_TASKS) idle, as in the reference).  Asynchronous, in order. */
+int flx_mk_reset(flx_ctx *ctx);          /* also zeroes the device RenderStats */
+int flx_mk_raygen(flx_ctx *ctx);
+int flx_mk_next_vertex(flx_ctx *ctx);
+int flx_mk_sample_bsdf(flx_ctx *ctx);
+int flx_mk_splat(flx_ctx *ctx);
+int flx_mk_splat_preview(flx_ctx *ctx);
+/* Device RenderStats {primary, extension, shadow rays, samples} the MK kernels maintain
+ * (CLContext::fetchStatsAsync, clcontext.cpp:660-664).  Synchronises. */
+int flx_mk_get_stats(flx_ctx *ctx, flx_render_stats *out);
+/* Tracer::renderSingle (tracer.cpp:108-182): `spp` times raygen -> (nextVertex -> sampleBsdf) x
+ * (maxBounces + 1) -> splat, replayed from a CUDA graph; do_reset != 0 runs flx_mk_reset first.
+ * Fails when maxBounces == 0 or Russian roulette is on (the reference switches it off, :118-122). */
+int flx_mk_render(flx_ctx *ctx, uint32_t spp, int do_reset);
+
 /* ---- results: CLContext::saveImage reads (clcontext.cpp:404-483), pickSingle (:934-949) ---------- */
 int flx_read_pixels(flx_ctx *ctx, int which /* flx_buffer */, void *host_out, size_t bytes); /* synchronises */
 void *flx_device_ptr(flx_ctx *ctx, int which /* flx_buffer */); /* for the per-frame all-reduce */

@@ -121,6 +121,14 @@ void orc_wf_logic(void *h, int firstIteration) { ((Wavefront *)h)->logic(firstIt
 void orc_wf_materials(void *h) { ((Wavefront *)h)->materials(); }
 void orc_wf_ext(void *h) { ((Wavefront *)h)->extRays(); }
 void orc_wf_shadow(void *h) { ((Wavefront *)h)->shadowRays(); }
+void orc_mk_reset(void *h) { ((Wavefront *)h)->mkReset(); }
+void orc_mk_raygen(void *h) { ((Wavefront *)h)->mkRaygen(); }
+void orc_mk_next_vertex(void *h) { ((Wavefront *)h)->mkNextVertex(); }
+void orc_mk_sample_bsdf(void *h) { ((Wavefront *)h)->mkSampleBsdf(); }
+void orc_mk_splat(void *h) { ((Wavefront *)h)->mkSplat(); }
+void orc_mk_splat_preview(void *h) { ((Wavefront *)h)->mkSplatPreview(); }
+void orc_mk_render_single(void *h, uint32_t spp) { ((Wavefront *)h)->mkRenderSingle(spp); }
+flx_render_stats *orc_mk_stats(void *h) { return &((Wavefront *)h)->stats; }
 void orc_wf_clear_queues(void *h) { ((Wavefront *)h)->clearQueues(); }
 void orc_wf_postprocess(void *h, float *outRGBA) { ((Wavefront *)h)->postprocess(outRGBA); }
 void orc_wf_update_pixel_index(void *h, uint32_t n) { ((Wavefront *)h)->updatePixelIndex(n); }

@@ -43,6 +43,16 @@ struct Wavefront
     void clearQueues();                 // CLContext::enqueueClearWfQueues
     void postprocess(float *outRGBA);   // mk_postprocess.cl
     void updatePixelIndex(uint32_t numNewPaths); // CLContext::updatePixelIndex
+
+    // microkernel renderer (o_microkernel.cpp): src/mk_*.cl, one task per pixel, phase word in slot 46
+    flx_render_stats stats = {0, 0, 0, 0};  // device RenderStats (mk_next_vertex.cl:44-56, mk_sample_bsdf.cl:97,127, mk_splat.cl:39)
+    void mkReset();                         // mk_reset.cl
+    void mkRaygen();                        // mk_raygen.cl
+    void mkNextVertex();                    // mk_next_vertex.cl
+    void mkSampleBsdf();                    // mk_sample_bsdf.cl
+    void mkSplat();                         // mk_splat.cl
+    void mkSplatPreview();                  // mk_splat_preview.cl
+    void mkRenderSingle(uint32_t spp);      // Tracer::renderSingle
 private:
     void materialQueue(int q, uint32_t len);
 };

@@ -48,7 +48,7 @@ def lib():
         L = C.CDLL(path)
         L.orc_wf_create.restype = V
         for name in ("orc_wf_state", "orc_wf_queue", "orc_wf_counters", "orc_wf_pixels", "orc_wf_spp",
-                     "orc_wf_denoiser_albedo", "orc_wf_denoiser_normal"):
+                     "orc_wf_denoiser_albedo", "orc_wf_denoiser_normal", "orc_mk_stats"):
             getattr(L, name).restype = V
         L.orc_wf_render.restype = U64
         L.orc_wf_get_pixel_index.restype = U32
@@ -157,6 +157,16 @@ class OracleWavefront:
     def update_pixel_index(self, n): self.L.orc_wf_update_pixel_index(self.h, U32(int(n)))
     def set_pixel_index(self, v): self.L.orc_wf_set_pixel_index(self.h, U32(int(v)))
     def get_pixel_index(self): return int(self.L.orc_wf_get_pixel_index(self.h))
+
+    # microkernel renderer (src/mk_*.cl): one task per pixel, phase word in state slot 46
+    def mk_reset(self): self.L.orc_mk_reset(self.h)
+    def mk_raygen(self): self.L.orc_mk_raygen(self.h)
+    def mk_next_vertex(self): self.L.orc_mk_next_vertex(self.h)
+    def mk_sample_bsdf(self): self.L.orc_mk_sample_bsdf(self.h)
+    def mk_splat(self): self.L.orc_mk_splat(self.h)
+    def mk_splat_preview(self): self.L.orc_mk_splat_preview(self.h)
+    def mk_render_single(self, spp): self.L.orc_mk_render_single(self.h, U32(int(spp)))
+    def mk_stats(self): return self._view(self.L.orc_mk_stats(self.h), (4,), np.uint32)
 
     def render(self, max_iterations, do_reset=True):
         st = np.zeros(4, np.uint64)

@@ -161,3 +161,59 @@ def test_benchmark_loop_pixel0_quirk(oracle, teapot, night_env):
         assert w[1:].min() >= spp and w.max() <= spp + 1  # `<=` admits maxSpp + 1 (quirk 3)
     finally:
         oracle.set_threads(oracle.max_threads())
+
+
+def _mk_params(teapot, W, H, **kw):
+    from fluctus_b200 import abi, scene as fs
+    return abi.make_render_params(W, H, n_tris=len(teapot["tris"]), world_radius=fs.world_radius(teapot), **kw)
+
+
+def test_microkernel_exact_spp_and_matches_wavefront(oracle, teapot, night_env):
+    """SURVEY.md §4 pair (3): the MK renderer (src/mk_*.cl, Tracer::renderSingle) gives every pixel exactly
+    `spp` samples, and its image agrees with the wavefront renderer's in the mean."""
+    W, H, SPP = 24, 16, 48
+    p = _mk_params(teapot, W, H, max_bounces=3, use_env_map=True, use_area_light=True)
+    mk = oracle.OracleWavefront(W * H, W, H)
+    mk.set_scene(teapot); mk.set_envmap(night_env); mk.set_params(p.tobytes())
+    mk.mk_render_single(SPP)
+    px = mk.pixels()
+    assert np.all(px[:, 3] == SPP)
+    st = mk.mk_stats()
+    assert st[3] == SPP * W * H and st[0] == SPP * W * H      # samples, primary rays
+    assert st[1] > 0 and st[2] > 0
+    assert np.all(mk.state()[46] == 5)                        # every task back in MK_GENERATE_CAMERA_RAY
+    assert np.isfinite(px).all()
+
+    wf = oracle.OracleWavefront(4096, W, H)
+    wf.set_scene(teapot); wf.set_envmap(night_env); wf.set_params(p.tobytes())
+    wf.render(200, True)
+    q = wf.pixels()
+    m_mk, m_wf = px[:, :3].sum(0) / px[:, 3].sum(), q[:, :3].sum(0) / q[:, 3].sum()
+    # MK samples BOTH lights at every vertex, WF picks one with probability 1/2 and divides by it: same mean
+    assert np.allclose(m_mk, m_wf, rtol=0.08), (m_mk, m_wf)
+
+
+def test_microkernel_phases_and_check_spp(oracle, teapot, night_env):
+    """Stage-by-stage phase machine (geom.h:205-216) and the CHECK_SPP branch of mk_splat.cl:21-32."""
+    W, H = 16, 8
+    p = _mk_params(teapot, W, H, max_bounces=2, use_env_map=True, use_area_light=False, max_spp=2)
+    mk = oracle.OracleWavefront(W * H + 40, W, H)               # NUM_TASKS > w*h: the extra tasks stay idle
+    mk.set_scene(teapot); mk.set_envmap(night_env); mk.set_params(p.tobytes())
+    mk.mk_reset()
+    ph = mk.state()[46]
+    assert np.all(ph[:W * H] == 5) and np.all(mk.state()[49][:W * H] == np.arange(W * H))
+    mk.mk_raygen()
+    assert np.all(ph[:W * H] == 0)
+    mk.mk_next_vertex()
+    assert set(np.unique(ph[:W * H])) <= {1, 4} and np.all(mk.state()[48][:W * H] == 1)
+    for s in range(5):
+        if s:
+            mk.mk_raygen()
+        for b in range(3):
+            mk.mk_next_vertex() if (s or b) else None
+            mk.mk_sample_bsdf()
+        assert set(np.unique(ph[:W * H])) <= {4, 6}
+        mk.mk_splat()
+    # `<=` on the pre-increment counter: maxSpp + 1 samples, then MK_DONE and the counter pinned to maxSpp
+    assert np.all(mk.pixels()[:, 3] == 3) and np.all(mk.spp() == 2) and np.all(ph[:W * H] == 6)
+    assert np.all(ph[W * H:] == 0) and np.all(mk.state()[48][W * H:] == 0)   # idle tasks untouched
