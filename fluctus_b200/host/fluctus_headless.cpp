@@ -2,11 +2,13 @@
 //
 // Replaces the reference's `Fluctus -b` batch mode (reference src/main.cpp:20-140 + Tracer::renderSingle,
 // src/tracer.cpp:108-182), which cannot run without a GLFW window and an OpenCL-GL context.  The command line
-// keeps the reference's flags (-x -y -s -b scenes...) and its settings.json surface; rendering uses the
-// wavefront loop (the path this backend accelerates) instead of the microkernel renderer.
+// keeps the reference's flags (-x -y -s -b scenes...) and its settings.json surface.  --renderer wavefront (default)
+// renders with the wavefront loop, the path this backend accelerates; --renderer mk runs Tracer::renderSingle as
+// the reference's batch mode does: the microkernel renderer, exactly SPP samples in every pixel, deterministic.
 //
 //   fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings settings.json] [--env map.hdr] [--bounces N]
-//                    [--iterations N] [--device D] [--out image.ppm|.pfm] [--save-scene out.flxs] scene...
+//                    [--renderer wavefront|mk] [--tasks N] [--iterations N] [--device D]
+//                    [--out image.ppm|.pfm] [--save-scene out.flxs] scene...
 //
 // scene: a .flxs container (host_scene.hpp) or — when built against the reference tree — any file the
 // reference's Scene::loadModel understands (.obj .ply .pbrt .pbf .sc.json), loaded and SBVH-built by the
@@ -21,7 +23,8 @@
 static void usage()
 {
     std::cerr << "usage: fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings FILE] [--env FILE.hdr] [--bounces N]\n"
-                 "                        [--iterations N] [--device D] [--out FILE.ppm|.pfm] [--save-scene FILE.flxs] scene...\n";
+                 "                        [--renderer wavefront|mk] [--tasks N] [--iterations N] [--device D]\n"
+                 "                        [--out FILE.ppm|.pfm] [--save-scene FILE.flxs] scene...\n";
 }
 
 static bool endsWith(const std::string &s, const std::string &e) { return s.size() >= e.size() && s.compare(s.size() - e.size(), e.size(), e) == 0; }
@@ -30,7 +33,8 @@ int main(int argc, char **argv)
 {
     flx::Settings settings;
     int width = -1, height = -1, spp = 32, device = 0, bounces = -1;
-    uint32_t iterations = 0;
+    uint32_t iterations = 0, tasks = 0;
+    bool useMK = false;
     std::string out = "output.ppm", saveScene, env;
     std::vector<std::string> scenes;
     try
@@ -49,6 +53,8 @@ int main(int argc, char **argv)
             else if (a == "--bounces") bounces = std::stoi(next());
             else if (a == "--iterations") iterations = (uint32_t)std::stoul(next());
             else if (a == "--device") device = std::stoi(next());
+            else if (a == "--renderer") { const std::string r = next(); if (r != "mk" && r != "wavefront") throw std::runtime_error("--renderer mk|wavefront"); useMK = (r == "mk"); }
+            else if (a == "--tasks") tasks = (uint32_t)std::stoul(next());
             else if (a == "--out") out = next();
             else if (a == "--save-scene") saveScene = next();
             else if (!a.empty() && a[0] == '-') throw std::runtime_error("unknown option " + a);
@@ -86,10 +92,21 @@ int main(int argc, char **argv)
             if (!saveScene.empty()) flx::saveScene(saveScene, scene);
 
             // Tracer::renderSingle disables Russian roulette for fixed-spp renders (src/tracer.cpp:117-121)
-            flx::HeadlessTracer tracer(width, height, settings, device);
+            flx::Settings sceneSettings = settings;
+            if (tasks) sceneSettings.wfBufferSize = tasks;
+            // the microkernel renderer keeps one task per pixel (mk_raygen.cl:8-9)
+            if (useMK && (uint64_t)sceneSettings.wfBufferSize < (uint64_t)width * height) sceneSettings.wfBufferSize = (uint32_t)(width * height);
+            flx::HeadlessTracer tracer(width, height, sceneSettings, device);
             tracer.init(scene);
             const auto t0 = std::chrono::steady_clock::now();
-            const flx::CudaContext::Totals t = tracer.render((uint32_t)spp, iterations ? iterations : (1u << 20));
+            flx::CudaContext::Totals t{};
+            if (useMK) // Tracer::renderSingle — what the reference's own `-b -s SPP` runs (src/main.cpp, tracer.cpp:108-182)
+            {
+                const flx::RenderStats st = tracer.renderSingle((uint32_t)spp);
+                t.primary = st.primaryRays; t.extension = st.extensionRays; t.shadow = st.shadowRays; t.samples = st.samples;
+                t.iterations = (uint64_t)spp;
+            }
+            else t = tracer.render((uint32_t)spp, iterations ? iterations : (1u << 20));
             const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
             std::string file = out;
             if (scenes.size() > 1) file = out.substr(0, out.rfind('.')) + "_" + std::to_string(si) + out.substr(out.rfind('.'));

@@ -215,6 +215,22 @@ public:
         return t;
     }
 
+    // Tracer::renderSingle (src/tracer.cpp:108-182): the reference's batch mode (`-b -s SPP`, src/main.cpp) — the
+    // microkernel renderer, every pixel gets exactly `spp` samples (this rank's share of them), Russian roulette
+    // off, deterministic image.  Needs wfBufferSize >= width * height (mk_raygen.cl:8-9).
+    RenderStats renderSingle(uint32_t spp)
+    {
+        if ((uint64_t)clctx.getNumTasks() < (uint64_t)params.width * params.height)
+            throw std::runtime_error("renderSingle: wfBufferSize must be >= width * height for the microkernel renderer");
+        if (params.useRoulette) { std::cout << "Turning off russian roulette" << std::endl; params.useRoulette = 0; }
+        clctx.updateParams(params);
+        const uint32_t ws = (uint32_t)worldSize, share = spp / ws + ((uint32_t)rank < spp % ws ? 1u : 0u);
+        clctx.renderSingle(share, true);
+        clctx.enqueuePostprocessKernel(params);
+        clctx.fetchStats();
+        return clctx.statsAsync;
+    }
+
     // CLContext::saveImage (src/clcontext.cpp:404-483).  ".ppm": tonemapped preview, clamp, (uchar)(255*x), flipped
     // vertically (the reference's image origin is bottom-left).  ".pfm": raw accumulation / sample count (the
     // reference's ".hdr" branch), float RGB, bottom-up as PFM defines it.

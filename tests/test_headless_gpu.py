@@ -62,3 +62,30 @@ def test_headless_render_matches_python_tracer_and_oracle(tmp_path, oracle, teap
     ppm = str(tmp_path / "img.ppm")
     r = subprocess.run([BIN, "-x", str(W), "-y", str(H), "-s", "2", "--settings", cfg, "--out", ppm, flxs], capture_output=True, text=True)
     assert r.returncode == 0 and os.path.getsize(ppm) == len("P6\n%d %d\n255\n" % (W, H)) + W * H * 3
+
+
+def test_headless_microkernel_mode_is_bit_identical_to_python_host(tmp_path, teapot, night_env):
+    """`--renderer mk` = Tracer::renderSingle (the reference's own batch mode): exact spp, deterministic — so the C++
+    host and the Python host must produce the same bits through the same C-ABI."""
+    from fluctus_b200 import Tracer, scene as fs
+    W, H, spp, bounces = 80, 48, 5, 3
+    flxs, out, cfg = str(tmp_path / "teapot.flxs"), str(tmp_path / "mk.pfm"), str(tmp_path / "settings.json")
+    fs.save_flxs(flxs, teapot, night_env)
+    json.dump({"release": {"wfBufferSize": 1024, "useAreaLight": True, "maxPathDepth": bounces, "useRussianRoulette": True}}, open(cfg, "w"))
+    r = subprocess.run([BIN, "-x", str(W), "-y", str(H), "-s", str(spp), "-b", "--renderer", "mk", "--settings", cfg, "--out", out, flxs],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "Turning off russian roulette" in r.stdout       # tracer.cpp:118-122
+    stats = json.loads(r.stdout.strip().splitlines()[-1])
+    assert stats["samples"] == spp * W * H == stats["primary"] and stats["iterations"] == spp
+    a = _read_pfm(out)
+
+    tr = Tracer(W, H, num_tasks=W * H, max_bounces=bounces, use_env_map=True, use_area_light=True, use_roulette=True)
+    tr.init(teapot, night_env)
+    st = tr.renderSingle(spp)
+    px = tr.pixels()
+    assert np.all(px[..., 3] == spp)
+    b = px[..., :3] / np.maximum(px[..., 3:], 1)
+    tr.close()
+    assert st["extensionRays"] == stats["extension"] and st["shadowRays"] == stats["shadow"]
+    assert np.array_equal(a.view(np.uint32), b.astype(np.float32).view(np.uint32))

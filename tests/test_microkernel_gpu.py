@@ -235,3 +235,29 @@ def test_mk_exact_spp_full_resolution_and_preview(teapot, night_env):
     assert np.all(pv[:, 3] == 0) and pv[:, :3].sum() > 0
     assert np.all(c.exportState()[46][:W * H] == 5)
     tr.close()
+
+
+def test_mk_against_committed_golden_image(teapot, night_env):
+    """The committed fixture (tests/golden/mk_golden.npz, frozen oracle output): RenderStats and phases exact, image
+    per pixel within the float tolerance."""
+    import os
+    from conftest import GOLDEN
+    from fluctus_b200 import CudaContext, abi
+    from fluctus_b200.context import BUF_PIXELS
+    g = np.load(os.path.join(GOLDEN, "mk_golden.npz"))
+    W, H = 48, 32
+    ctx = CudaContext(num_tasks=W * H)
+    ctx.uploadSceneData(teapot); ctx.createEnvMap(night_env)
+    ctx.updateParams(np.frombuffer(g["params"].tobytes(), abi.PARAMS_DT))
+    ctx.renderSingle(int(g["spp"]))
+    st = ctx.getStats()
+    assert st["samples"] == int(g["stats"][3]) and st["primaryRays"] == int(g["stats"][0])
+    assert abs(st["extensionRays"] - int(g["stats"][1])) <= 4 and abs(st["shadowRays"] - int(g["stats"][2])) <= 8
+    px, ref = ctx.readPixels(BUF_PIXELS).astype(np.float64), g["pixels"].astype(np.float64)
+    assert np.array_equal(px[:, 3], ref[:, 3])
+    rel = np.abs(px[:, :3] - ref[:, :3]).max(1) / np.maximum(np.abs(ref[:, :3]).max(1), 1e-3)
+    assert (rel > 1e-4).mean() <= 0.01 and (rel > 1e-5).mean() <= 0.05, ((rel > 1e-4).sum(), (rel > 1e-5).sum())
+    rows = list(g["rows"])
+    assert np.array_equal(ctx.exportState()[46], g["state_rows"][rows.index(46)])       # phase
+    assert (ctx.exportState()[49] != g["state_rows"][rows.index(49)]).mean() <= 2e-3    # seed: same number of RNG draws
+    ctx.close()

@@ -217,3 +217,19 @@ def test_microkernel_phases_and_check_spp(oracle, teapot, night_env):
     # `<=` on the pre-increment counter: maxSpp + 1 samples, then MK_DONE and the counter pinned to maxSpp
     assert np.all(mk.pixels()[:, 3] == 3) and np.all(mk.spp() == 2) and np.all(ph[:W * H] == 6)
     assert np.all(ph[W * H:] == 0) and np.all(mk.state()[48][W * H:] == 0)   # idle tasks untouched
+
+
+def test_microkernel_golden_image(oracle, teapot, night_env):
+    """tests/golden/mk_golden.npz (tools/make_golden_vectors.py mk): renderSingle state, image and RenderStats."""
+    g = np.load(os.path.join(GOLDEN, "mk_golden.npz"))
+    W, H = 48, 32
+    oracle.set_threads(1)
+    try:
+        mk = oracle.OracleWavefront(W * H, W, H)
+        mk.set_scene(teapot); mk.set_envmap(night_env); mk.set_params(g["params"].tobytes())
+        mk.mk_render_single(int(g["spp"]))
+        assert np.array_equal(mk.mk_stats(), g["stats"])
+        assert np.array_equal(mk.state()[g["rows"]], g["state_rows"])
+        assert np.array_equal(bits(mk.pixels()), bits(g["pixels"]))
+    finally:
+        oracle.set_threads(oracle.max_threads())

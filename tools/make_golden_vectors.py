@@ -5,7 +5,8 @@ these files do NOT pin the oracle to the reference: they freeze the oracle's own
 self-consistency checks: stack == bit-stack == brute force) so that any later change to the oracle
 or to the CUDA kernels is detected on a box that has neither /root/reference nor a compiler.
 
-    python tools/make_golden_vectors.py      # rewrites tests/golden/trace_golden.npz, wf_golden.npz
+    python tools/make_golden_vectors.py [mk]   # rewrites tests/golden/trace_golden.npz, wf_golden.npz, mk_golden.npz
+                                               # ("mk": only the microkernel file, the others stay byte-identical)
 """
 import os
 import sys
@@ -40,10 +41,29 @@ def special_rays(bounds):
     return np.asarray(rows, np.float32)
 
 
+def microkernel(teapot, env):
+    # microkernel renderer: Tracer::renderSingle, 3 spp at 48x32, both lights, serial
+    W, H, SPP = 48, 32, 3
+    p = abi.make_render_params(W, H, n_tris=len(teapot["tris"]), world_radius=fs.world_radius(teapot), max_bounces=3,
+                               use_env_map=True, use_area_light=True, cam_pos=(0.0, 0.2, 1.3))  # the teapot fills the frame
+    mk = pyoracle.OracleWavefront(W * H, W, H)
+    mk.set_scene(teapot); mk.set_envmap(env); mk.set_params(p.tobytes())
+    mk.mk_render_single(SPP)
+    fields = ("orig", "dir", "T", "Ei", "P", "N", "uvTex", "phase", "lastPdfW", "pathLen", "seed", "lastSpecular", "t", "i", "matId")
+    rows = sorted(set(r for f in fields for r in range(abi.SLOTS[f], abi.SLOTS[f] + abi.SLOT_WIDTH.get(f, 1))))
+    np.savez_compressed(os.path.join(GOLD, "mk_golden.npz"), params=p.view(np.uint8), spp=np.uint32(SPP), rows=np.array(rows, np.int32),
+                        state_rows=mk.state()[rows].copy(), pixels=mk.pixels().copy(), stats=mk.mk_stats().copy())
+    print("mk_golden:", mk.mk_stats(), "mean", mk.pixels()[:, :3].sum(0) / mk.pixels()[:, 3].sum())
+
+
 def main():
     teapot = fs.load_scene(os.path.join(GOLD, "teapot_sbvh.npz"))
     env = fs.load_envmap(os.path.join(GOLD, "night_env.npz"))
     pyoracle.set_threads(1)
+    if sys.argv[1:] == ["mk"]:
+        microkernel(teapot, env)
+        pyoracle.set_threads(pyoracle.max_threads())
+        return
 
     rays = np.concatenate([fs.bench_rays(4096, teapot["bounds"]), special_rays(teapot["bounds"])])
     out = {}
@@ -73,6 +93,7 @@ def main():
                         pixels=wf.pixels().copy(), preview=wf.postprocess(), stats=np.array([st[k] for k in ("primary", "extension", "shadow", "samples")], np.uint64),
                         pixel_index=np.uint32(wf.get_pixel_index()))
     print("wf_golden:", st, "pixel index", wf.get_pixel_index())
+    microkernel(teapot, env)
     pyoracle.set_threads(pyoracle.max_threads())
 
 
