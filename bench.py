@@ -201,14 +201,14 @@ def run_reference_arm(args):
     val = samples / dt / 1e6
     sample = ("%d steps x %d steady-state iterations of a %d-path pool after %d ramp-up iterations"
               % (args.steps, CPU_ITERS_PER_STEP, CPU_TASKS, CPU_RAMP_ITERS))
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_dict(args.gpus, scene, "reference"),
         "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": cw.threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0})
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -432,10 +432,21 @@ def run_ours(args):
             "events_pass_ms_per_step": r["ms"] / args.steps,
             "clocks": clk, "cpu_baseline": cpu, "raycast": raycast,
         }
-        print(json.dumps(line))
+        emit(line)
     tr.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+_RESULT_FD = None
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
 
 
 def main():
@@ -447,6 +458,12 @@ def main():
     ap.add_argument("--no-raycast", action="store_true", help="skip the cfg5 ray-cast microbench")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON result: libraries that write to fd 1 on their own (NCCL prints its
+    # version banner there when NCCL_DEBUG is set) are sent to stderr for the duration of the run.
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference_arm(args)
     else:
