@@ -48,6 +48,7 @@ CPU_RAMP_ITERS = 14          # untimed iterations that bring the CPU pool to ste
 METRIC = "Msamples/s (1080p kitchen, 8 bounces)"
 # algorithmic bytes of one extension-ray traversal
 B_RAY_IN, B_RAY_OUT, B_INNER, B_TRI, B_HIT = 28, 56, 56, 40, 64
+B_SHADOW_STATE = 36  # `shadow` state per ray (queue index, origin + length, direction, blocked flag)
 
 
 def load_workload():
@@ -213,10 +214,15 @@ def run_reference_arm(args):
 
 # ---------------------------------------------------------------------------------------------------
 # GPU arm
-def traversal_bytes(cnt, rays=None):
-    """Algorithmic bytes of SURVEY.md §8(d) for `rays` rays with the per-ray visit statistics of cnt."""
+def traversal_bytes(cnt, rays=None, any_hit=False):
+    """Algorithmic bytes of SURVEY.md §8(d) for `rays` rays with the per-ray visit statistics of cnt.
+    any_hit: shadow rays — 36 B of path state per ray (queue index, origin + length, direction, result word), no
+    shading fetch."""
     r = max(int(cnt["rays"]), 1)
-    per_ray = (B_RAY_IN + B_RAY_OUT) + (cnt["inner"] * B_INNER + cnt["tri"] * B_TRI + cnt["hits"] * B_HIT) / r
+    if any_hit:
+        per_ray = B_SHADOW_STATE + (cnt["inner"] * B_INNER + cnt["tri"] * B_TRI) / r
+    else:
+        per_ray = (B_RAY_IN + B_RAY_OUT) + (cnt["inner"] * B_INNER + cnt["tri"] * B_TRI + cnt["hits"] * B_HIT) / r
     return per_ray * (r if rays is None else rays), per_ray
 
 
@@ -397,10 +403,13 @@ def run_ours(args):
     cnt = c.traceCounters()
     c.setTraceCounting(False)
     peak, peak_src = measured_peak_gbs()
+    # the render entry traces the extension and the shadow rays of an iteration in ONE persistent launch
+    # (k_ext_shadow); its events are filed under the extension stage
     ext_ms, ext_n = r["stage"]["ext"]
     ext_bytes, ext_per_ray = traversal_bytes(cnt["ext"], rays=r["local"]["extension"])
-    ext_achieved = ext_bytes / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
-    stage_ms = {k: s[0] for k, s in r["stage"].items()}
+    shw_bytes, shw_per_ray = traversal_bytes(cnt["shadow"], rays=r["local"]["shadow"], any_hit=True)
+    trace_achieved = (ext_bytes + shw_bytes) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
+    stage_ms = {("trace" if k == "ext" else k): s[0] for k, s in r["stage"].items() if k not in ("shadow", "raygen") or s[0] > 0}
     stage_sum = sum(stage_ms.values())
 
     raycast = None
@@ -421,10 +430,12 @@ def run_ours(args):
             "e2e": {"value": h["samples"] / (h["ms"] * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": h["ms"] / args.steps,
                     "h2d_bytes_per_step": 256, "d2h_bytes_per_step": n_px * 16 + 48},
             "gpu_launches": int(v["launches"]),
-            "roofline": {"bound": "hbm", "kernel": "k_ext (extension-ray closest-hit traversal)", "achieved": ext_achieved,
-                         "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": ext_achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": "k_ext_shadow (extension closest-hit + shadow any-hit traversal of one iteration, one persistent launch)",
+                         "achieved": trace_achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                         "frac": trace_achieved / peak, "traffic": None,
                          "launches": int(ext_n), "avg_launch_ms": ext_ms / max(ext_n, 1),
-                         "algorithmic_bytes_per_ray": ext_per_ray,
+                         "algorithmic_bytes_per_ray": {"extension": ext_per_ray, "shadow": shw_per_ray},
+                         "rays_per_launch": {"extension": r["local"]["extension"] / max(ext_n, 1), "shadow": r["local"]["shadow"] / max(ext_n, 1)},
                          "share_of_step": ext_ms / stage_sum if stage_sum else None,
                          "timed_in": "the same K frames repeated launch by launch right after the graph-replayed region, "
                                      "CUDA events around every stage launch on the context's stream"},

@@ -42,15 +42,20 @@ int stageRaygen(flx_ctx *ctx) { TimerScope t(ctx, 3); return flx_launch_raygen(c
 int stageMaterials(flx_ctx *ctx) { TimerScope t(ctx, 4); return flx_launch_materials(ctx); }
 int stageExt(flx_ctx *ctx) { TimerScope t(ctx, 0); return flx_launch_ext(ctx); }
 int stageShadow(flx_ctx *ctx) { TimerScope t(ctx, 1); return flx_launch_shadow(ctx); }
+int stageExtShadow(flx_ctx *ctx) { TimerScope t(ctx, 0); return flx_launch_ext_shadow(ctx); } // timed under the extension stage
 
 // one pass of the reference's benchmark inner loop (tracer.cpp:737-778)
 int enqueueIteration(flx_ctx *ctx)
 {
     FLX_TRY(stageLogicRegen(ctx)); // logic + raygen: terminated paths restart inside the logic kernel
     FLX_TRY(stageMaterials(ctx));
-    FLX_TRY(stageExt(ctx));
-    FLX_TRY(stageShadow(ctx));
-    FLX_TRY(flx_launch_bookkeeping(ctx)); // getCounters + clear + updatePixelIndex, on the device
+    if (ctx->counting) // the visit counters are kept per stage
+    {
+        FLX_TRY(stageExt(ctx));
+        FLX_TRY(stageShadow(ctx));
+        FLX_TRY(flx_launch_bookkeeping(ctx)); // getCounters + clear + updatePixelIndex, on the device
+    }
+    else FLX_TRY(stageExtShadow(ctx)); // both ray stages + the bookkeeping (last CTA) in one persistent launch
     return FLX_OK;
 }
 
@@ -127,6 +132,7 @@ int flx_render(flx_ctx *ctx, uint32_t iterations, int do_reset)
         FLX_TRY(stageExt(ctx));
     }
     if (iterations == 0) return FLX_OK;
+    FLX_TRY(flx_reset_trace_cursors(ctx)); // k_ext_shadow expects (and leaves) them zero; a stage call may have used them
     if (ctx->timing) // per-stage events need individual launches
     {
         for (uint32_t i = 0; i < iterations; i++) FLX_TRY(enqueueIteration(ctx));

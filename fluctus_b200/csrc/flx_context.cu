@@ -94,7 +94,7 @@ int flx_create(flx_ctx **out, int device, uint32_t num_tasks, void *cuda_stream)
         for (int i = 0; i < FLX_NUM_QUEUES; i++) ctx->qs.q[i] = q + (size_t)i * N;
         uint8_t *tail = (uint8_t *)(q + (size_t)FLX_NUM_QUEUES * N);
         ctx->qs.counters = (flx_queue_counters *)tail;       // 40 B
-        ctx->dPixelIdx = (uint32_t *)(tail + 64);            // pixel cursor + 2 work cursors
+        ctx->dPixelIdx = (uint32_t *)(tail + 64);            // pixel cursor + 2 work cursors + CTA arrival counter
         ctx->dTotals = (RenderTotals *)(tail + 128);         // 48 B
         ctx->dStats = (flx_render_stats *)(tail + 192);      // 16 B
         ctx->dTraceStats = (unsigned long long *)(tail + 256); // 20 x u64

@@ -75,6 +75,24 @@ struct RenderTotals
     unsigned long long primary, extension, shadow, samples, splatted, iterations;
 };
 
+// Closes one iteration on the device: queue lengths -> statistics, pixel cursor advanced by the number of
+// regenerated paths, counters cleared.  Called by ONE thread (k_bookkeeping, or the last CTA of k_ext_shadow).
+#ifdef __CUDACC__
+static __device__ __forceinline__ void closeIteration(flx_queue_counters *counters, RenderTotals *totals, uint32_t *pixelIdx, uint32_t numPixels)
+{
+    const flx_queue_counters c = *counters;
+    totals->primary += c.raygenQueue;
+    totals->extension += c.extensionQueue;
+    totals->shadow += c.shadowQueue;
+    totals->samples += (totals->iterations > 0) ? c.raygenQueue : 0u;
+    totals->splatted += c.splattedSamples;
+    totals->iterations += 1;
+    *pixelIdx = (*pixelIdx + c.raygenQueue) % numPixels;
+    flx_queue_counters z = {};
+    *counters = z;
+}
+#endif
+
 struct StageTimer
 {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
@@ -144,6 +162,8 @@ int flx_repack_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, cons
                      const flx_node *nodes, size_t n_nodes);
 int flx_launch_ext(flx_ctx *ctx);
 int flx_launch_shadow(flx_ctx *ctx);
+int flx_launch_ext_shadow(flx_ctx *ctx); // both in one persistent launch + the iteration's bookkeeping (render entry)
+int flx_reset_trace_cursors(flx_ctx *ctx);
 int flx_launch_trace_batch(flx_ctx *ctx, const float4 *dRays, size_t n, int32_t *dHitI, float *dHitT, flx_hit *dHits);
 int flx_launch_any_batch(flx_ctx *ctx, const float4 *dRays, size_t n, uint8_t *dOcc);
 

@@ -84,6 +84,7 @@ struct ShadowJob
     FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
     {
         gid = queue[k];
+        nRays++;
         const float4 s0 = st.shw0[gid];
         o = mk3(s0); d = mk3(st.shw1[gid]); tmax = s0.w;
         if (params.useAreaLight) // the light quad occludes from its front side (wf_shadowrays.cl:31-33)
@@ -95,7 +96,7 @@ struct ShadowJob
     }
     FLX_DEV void store(const RayHit &h, f3, f3)
     {
-        nRays++; nHits += (h.slot >= 0);
+        nHits += (h.slot >= 0);
         st.shadowBlocked[gid] = h.slot >= 0 ? 1u : 0u;
     }
 };
@@ -223,6 +224,47 @@ k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
+// Extension and shadow rays of one iteration in ONE persistent launch (render entry).  The two stages are
+// independent (extension rays read ray0/ray1 and write the hit record, shadow rays read shw0/shw1 and write
+// shadowBlocked), so a warp that finds the extension pool empty moves straight on to the shadow pool instead of
+// idling until the slowest extension ray of the grid has finished; the top of the tree is staged once.
+__global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
+k_ext_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ extQueue, const uint32_t *__restrict__ shadowQueue,
+             flx_queue_counters *counters, unsigned int *cursors, RenderTotals *totals, uint32_t *pixelIdx, uint32_t ownedPixels,
+             const __grid_constant__ flx_render_params params)
+{
+    extern __shared__ float4 topNodes[];
+    const unsigned int nExt = counters->extensionQueue, nShadow = counters->shadowQueue;
+    if (nExt != 0u || nShadow != 0u)
+    {
+        stageTopNodes(bvh, topNodes);
+        TravCount cnt = {0u, 0u, 0u};
+        if (nExt)
+        {
+            ExtJob job = {bvh, st, extQueue, params, 0u, 0u, 0u};
+            traceLoop<false, false>(bvh, topNodes, job, cursors, nExt, cnt);
+        }
+        if (nShadow)
+        {
+            ShadowJob job = {st, shadowQueue, params, 0u, 0u, 0u};
+            traceLoop<true, false>(bvh, topNodes, job, cursors + 1, nShadow, cnt);
+        }
+    }
+    // The CTA that finishes last closes the iteration: what the reference's host does between iterations
+    // (statistics src/tracer.cpp:761-765, updatePixelIndex + enqueueClearWfQueues src/clcontext.cpp:903-921) and
+    // the reset of the two work cursors.  Every CTA has read the counters before it arrives here.
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        __threadfence();
+        if (atomicAdd(cursors + 2, 1u) == gridDim.x - 1u)
+        {
+            closeIteration(counters, totals, pixelIdx, ownedPixels);
+            cursors[0] = 0u; cursors[1] = 0u; cursors[2] = 0u;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_mk_vertex(DevBVH bvh, PathState st, unsigned int total, unsigned int *cursor, const __grid_constant__ flx_render_params params)
 {
@@ -282,7 +324,7 @@ static cudaError_t traceKernelSetup(flx_ctx *ctx)
     if (ctx->traceSetupDone) return cudaSuccess;
     const void *kernels[] = {(const void *)k_ext<false>, (const void *)k_ext<true>, (const void *)k_shadow<false>, (const void *)k_shadow<true>,
                              (const void *)k_trace_batch<false>, (const void *)k_trace_batch<true>, (const void *)k_any_batch<false>, (const void *)k_any_batch<true>,
-                             (const void *)k_mk_vertex, (const void *)k_mk_shadow<false>, (const void *)k_mk_shadow<true>};
+                             (const void *)k_ext_shadow, (const void *)k_mk_vertex, (const void *)k_mk_shadow<false>, (const void *)k_mk_shadow<true>};
     for (const void *k : kernels)
     {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FLX_TOP_SMEM_BYTES);
@@ -292,7 +334,7 @@ static cudaError_t traceKernelSetup(flx_ctx *ctx)
     return cudaSuccess;
 }
 
-// cursors live right behind the pixel cursor: [1] ext, [2] shadow / batch
+// cursors live right behind the pixel cursor: [1] ext, [2] shadow / batch, [3] CTA arrival counter of k_ext_shadow
 static unsigned int *workCursor(flx_ctx *ctx, int which) { return (unsigned int *)(ctx->dPixelIdx + 1 + which); }
 
 #define FLX_LAUNCHED(ctx) do { (ctx)->launches++; FLX_CUDA(ctx, cudaGetLastError()); } while (0)
@@ -306,6 +348,22 @@ int flx_launch_ext(flx_ctx *ctx)
         k_ext<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, ctx->dTraceStats, ctx->params);
     else
         k_ext<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, nullptr, ctx->params);
+    FLX_LAUNCHED(ctx);
+    return FLX_OK;
+}
+
+// zero the work cursors and the arrival counter of k_ext_shadow (which leaves them zero again when it ends)
+int flx_reset_trace_cursors(flx_ctx *ctx)
+{
+    FLX_CUDA(ctx, cudaMemsetAsync(workCursor(ctx, 0), 0, 3 * sizeof(unsigned int), ctx->stream));
+    return FLX_OK;
+}
+
+int flx_launch_ext_shadow(flx_ctx *ctx)
+{
+    FLX_CUDA(ctx, traceKernelSetup(ctx));
+    k_ext_shadow<<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.q[FLX_Q_SHADOW],
+        ctx->qs.counters, workCursor(ctx, 0), ctx->dTotals, ctx->dPixelIdx, flx_owned_pixels(ctx), ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }

@@ -103,16 +103,7 @@ k_postprocess(FrameBuffers fb, float exposure, uint32_t tmOperator, int denoiser
 // paths, zero the counters.  One thread; keeps flx_render free of host synchronisation.
 __global__ void k_bookkeeping(flx_queue_counters *counters, RenderTotals *totals, uint32_t *pixelIdx, uint32_t numPixels)
 {
-    const flx_queue_counters c = *counters;
-    totals->primary += c.raygenQueue;
-    totals->extension += c.extensionQueue;
-    totals->shadow += c.shadowQueue;
-    totals->samples += (totals->iterations > 0) ? c.raygenQueue : 0u;
-    totals->splatted += c.splattedSamples;
-    totals->iterations += 1;
-    *pixelIdx = (*pixelIdx + c.raygenQueue) % numPixels;
-    flx_queue_counters z = {};
-    *counters = z;
+    closeIteration(counters, totals, pixelIdx, numPixels);
 }
 
 __global__ void k_advance_pixel(uint32_t *pixelIdx, uint32_t numPixels, uint32_t numNew)
