@@ -8,17 +8,18 @@
 Workload (BASELINE.json metric "Msamples/s (1080p kitchen, 8 bounces)", configs[3]): the kitchen
 stand-in scene (Country-Kitchen.obj is stripped from the reference snapshot, SURVEY.md §7.3.7;
 fluctus_b200/standin.py rebuilds a room with the kitchen's material mix from the committed teapot
-fixture), 1920x1080, 8 bounces, environment-map MIS + area light, NUM_TASKS = 2^20 paths per GPU.
+fixture), 1920x1080, 8 bounces, environment-map MIS + area light, NUM_TASKS = 2^22 paths per GPU.
 
-One STEP = one frame: reset, ITERS wavefront iterations (logic -> raygen -> materials -> ext ->
-shadow -> bookkeeping, the reference's benchmark inner loop, src/tracer.cpp:737-778), one
+One STEP = one frame: reset, ITERS wavefront iterations (logic+raygen -> materials -> ext+shadow+
+bookkeeping: the reference's benchmark inner loop, src/tracer.cpp:737-778, in three launches), one
 all-reduce of the float accumulation buffer over the ranks, tonemap.  Per-GPU work is fixed as N
 grows (each rank traces its own N paths with rank-offset seeds): weak scaling.
   value : Msamples/s, device-resident, CUDA events around K graph-replayed steps, max over ranks
           (the K steps are then repeated launch by launch with events around every stage: stage times, roofline)
   e2e   : the same frame through the public API with host buffers: RenderParams uploaded and
           the tonemapped frame + counters read back to pinned host memory inside the timed region
-  roofline : extension-ray traversal kernel (k_ext), algorithmic bytes of SURVEY.md §8(d) / DESIGN.md
+  roofline : the traversal launch (k_ext_shadow: extension closest-hit + shadow any-hit rays of an iteration),
+          algorithmic bytes of SURVEY.md §8(d) / DESIGN.md
   cpu_baseline / --impl reference : the CPU restatement of the reference's OpenCL kernels
           (oracle/, OpenMP over work-items) on the host cores — the reference's own device code
           needs an OpenCL runtime that does not exist on this box.
@@ -39,7 +40,11 @@ if ROOT not in sys.path:
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 WIDTH, HEIGHT = 1920, 1080
-NUM_TASKS = 1 << 20
+# wfBufferSize ("the amount of paths in flight simultaneously, limited by VRAM", clcontext.hpp:93; default 2^20 in
+# settings.cpp:26).  On a 180 GB B200 the pool is 2^22 paths (0.87 GB of state + 0.15 GB of queues): the persistent
+# traversal launch ends with a tail in which a few long rays keep the GPU waiting, and a 4x larger pool amortises
+# it (measured: 2^20 145, 2^21 153, 2^22 157, 2^23 158 Msamples/s).  FLX_BENCH_TASKS overrides it for experiments.
+NUM_TASKS = int(os.environ.get("FLX_BENCH_TASKS", 1 << 22))
 MAX_BOUNCES = 8
 ITERS_PER_STEP = 48          # wavefront iterations per frame
 CPU_TASKS = 1 << 18          # path pool of the CPU arm (throughput per path does not depend on it)
