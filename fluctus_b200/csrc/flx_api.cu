@@ -310,27 +310,13 @@ int flx_trace_any(flx_ctx *ctx, const float *rays, size_t n, uint8_t *occluded)
 // given NDC point.  The ray set-up (kernel_pick.cl:12-24) is a dozen flops, done here on the host.
 int flx_pick(flx_ctx *ctx, float ndc_x, float ndc_y, flx_hit *out)
 {
-    FLX_CHECK_CTX(ctx);
+    FLX_CHECK_CTX(ctx); FLX_CUDA(ctx, cudaSetDevice(ctx->device));
     if (!out) return flx_fail(ctx, FLX_ERR_ARG, "flx_pick: null output");
     FLX_TRY(flx_ready(ctx, true));
-    const flx_render_params &p = ctx->params;
-    volatile float scrx = ndc_x + ndc_x - 1.0f, scry = ndc_y + ndc_y - 1.0f; // volatile: no host-side contraction
-    scrx = scrx * ((float)p.width * p.height1);
-    scrx = scrx * p.camera.fovSCALE; scry = scry * p.camera.fovSCALE;
-    float d[3];
-    const float *pos = &p.camera.pos.x, *right = &p.camera.right.x, *up = &p.camera.up.x, *dir = &p.camera.dir.x;
-    for (int k = 0; k < 3; k++)
-    {
-        volatile float a = right[k] * scrx, b = up[k] * scry;
-        volatile float tgt = pos[k] + a; tgt = tgt + b; tgt = tgt + dir[k];
-        d[k] = tgt - pos[k];
-    }
-    volatile float l2 = d[0] * d[0]; { volatile float t = d[1] * d[1]; l2 = l2 + t; t = d[2] * d[2]; l2 = l2 + t; }
-    const float inv = 1.0f / sqrtf(l2);
-    float ray[8] = {pos[0], pos[1], pos[2], 3.402823466e+38f, d[0] * inv, d[1] * inv, d[2] * inv, 0.0f};
-    FLX_TRY(flx_trace_closest(ctx, ray, 1, nullptr, nullptr, out));
-    // area light as an implicit hit (kernel_pick.cl:28) is reported by the wavefront ext stage only
-    return FLX_OK;
+    FLX_TRY(ensureScratch(ctx, sizeof(flx_hit)));
+    FLX_TRY(flx_launch_pick(ctx, ndc_x, ndc_y, (flx_hit *)ctx->dScratch)); // ray set-up, trace and light test on the device
+    FLX_CUDA(ctx, cudaMemcpyAsync(out, ctx->dScratch, sizeof(flx_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    return flx_finish(ctx);
 }
 
 // ---- state inspection ---------------------------------------------------------------------------------

@@ -166,6 +166,7 @@ int flx_launch_ext_shadow(flx_ctx *ctx); // both in one persistent launch + the 
 int flx_reset_trace_cursors(flx_ctx *ctx);
 int flx_launch_trace_batch(flx_ctx *ctx, const float4 *dRays, size_t n, int32_t *dHitI, float *dHitT, flx_hit *dHits);
 int flx_launch_any_batch(flx_ctx *ctx, const float4 *dRays, size_t n, uint8_t *dOcc);
+int flx_launch_pick(flx_ctx *ctx, float ndcX, float ndcY, flx_hit *dHit);
 
 int flx_launch_mk_vertex_trace(flx_ctx *ctx, uint32_t total);
 int flx_launch_mk_shadow_trace(flx_ctx *ctx, uint32_t total, int lightOccludes);

@@ -140,6 +140,44 @@ struct MkShadowJob
     FLX_DEV void store(const RayHit &h, f3, f3) { st.shadowBlocked[gid] = h.slot >= 0 ? 1u : 0u; }
 };
 
+// kernel_pick.cl:6-41: the ray through NDC point (x, y) from the camera position (no lens sample), closest hit,
+// the light quad as an implicit hit when sampleImpl && useAreaLight; result as a Hit record (geom.h:152-163)
+struct PickJob
+{
+    const DevBVH &bvh; const flx_render_params &params; float ndcX, ndcY; float4 *out;
+    FLX_DEV bool load(unsigned int, f3 &o, f3 &d, float &tmax)
+    {
+        float SCRx = ndcX + ndcX - 1.0f;
+        float SCRy = ndcY + ndcY - 1.0f;
+        SCRx *= (float)params.width * params.height1;
+        SCRx *= params.camera.fovSCALE;
+        SCRy *= params.camera.fovSCALE;
+        const f3 pos = mk3(params.camera.pos.x, params.camera.pos.y, params.camera.pos.z);
+        const f3 right = mk3(params.camera.right.x, params.camera.right.y, params.camera.right.z);
+        const f3 up = mk3(params.camera.up.x, params.camera.up.y, params.camera.up.z);
+        const f3 dir = mk3(params.camera.dir.x, params.camera.dir.y, params.camera.dir.z);
+        const f3 rayTarget = pos + right * SCRx + up * SCRy + dir;
+        o = pos; d = normalize(rayTarget - pos); tmax = FLX_FLT_MAX;
+        return true;
+    }
+    FLX_DEV void store(const RayHit &h, f3 o, f3 d)
+    {
+        f3 P = mk3(0.0f), N = mk3(0.0f);
+        float uvx = 0.0f, uvy = 0.0f, t = FLX_FLT_MAX;
+        int hi = -1, matId = -1, al = 0;
+        if (h.slot >= 0) { t = h.t; fetchHitAttribs(bvh, h, o, d, hi, matId, P, N, uvx, uvy); }
+        if (params.sampleImpl && params.useAreaLight)
+        {
+            const AreaLightGeom g = makeLightGeom(params.areaLight);
+            if (intersectLight(g, o, d, t)) { al = 1; P = o + t * d; N = g.N; hi = 0; matId = 0; }
+        }
+        out[0] = mk4(P, 0.0f);
+        out[1] = mk4(N, 0.0f);
+        out[2] = make_float4(uvx, uvy, t, __int_as_float(hi));
+        out[3] = make_float4(__int_as_float(al), __int_as_float(matId), 0.0f, 0.0f);
+    }
+};
+
 // ray batch, closest hit: rays as 2 x float4 {o.xyz, tmax} {d.xyz, -}
 struct BatchJob
 {
@@ -286,6 +324,16 @@ k_mk_shadow(DevBVH bvh, PathState st, unsigned int total, unsigned int *cursor, 
     traceLoop<true, false>(bvh, topNodes, job, cursor, total, cnt);
 }
 
+__global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
+k_pick(DevBVH bvh, float ndcX, float ndcY, float4 *out, unsigned int *cursor, const __grid_constant__ flx_render_params params)
+{
+    extern __shared__ float4 topNodes[];
+    stageTopNodes(bvh, topNodes);
+    PickJob job = {bvh, params, ndcX, ndcY, out};
+    TravCount cnt = {0u, 0u, 0u};
+    traceLoop<false, false>(bvh, topNodes, job, cursor, 1u, cnt);
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
@@ -316,7 +364,10 @@ k_any_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigne
 // One persistent CTA of 1024 threads per SM: a single 55 KB copy of the top of the tree per SM.  Smaller CTAs
 // need one copy each, and the shared-memory carve-out then eats the L1 the deeper nodes and the triangles live
 // in (8 x 28 KB copies cost 8 % on the kitchen render and 17 % on incoherent rays; tools/tune_vote.sh).
-static int traceGrid(const flx_ctx *ctx) { return ctx->numSMs * (1024 / FLX_TRACE_THREADS); }
+#ifndef FLX_TRACE_CTAS_PER_SM
+#define FLX_TRACE_CTAS_PER_SM ((1024 / FLX_TRACE_THREADS) > FLX_TRACE_MIN_BLOCKS ? (1024 / FLX_TRACE_THREADS) : FLX_TRACE_MIN_BLOCKS)
+#endif
+static int traceGrid(const flx_ctx *ctx) { return ctx->numSMs * FLX_TRACE_CTAS_PER_SM; }
 
 // dynamic shared memory above 48 KB has to be opted into, per kernel and per device
 static cudaError_t traceKernelSetup(flx_ctx *ctx)
@@ -324,7 +375,7 @@ static cudaError_t traceKernelSetup(flx_ctx *ctx)
     if (ctx->traceSetupDone) return cudaSuccess;
     const void *kernels[] = {(const void *)k_ext<false>, (const void *)k_ext<true>, (const void *)k_shadow<false>, (const void *)k_shadow<true>,
                              (const void *)k_trace_batch<false>, (const void *)k_trace_batch<true>, (const void *)k_any_batch<false>, (const void *)k_any_batch<true>,
-                             (const void *)k_ext_shadow, (const void *)k_mk_vertex, (const void *)k_mk_shadow<false>, (const void *)k_mk_shadow<true>};
+                             (const void *)k_ext_shadow, (const void *)k_pick, (const void *)k_mk_vertex, (const void *)k_mk_shadow<false>, (const void *)k_mk_shadow<true>};
     for (const void *k : kernels)
     {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FLX_TOP_SMEM_BYTES);
@@ -414,6 +465,17 @@ int flx_launch_trace_batch(flx_ctx *ctx, const float4 *dRays, size_t n, int32_t 
         k_trace_batch<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 10, dHitI, dHitT, (float4 *)dHits);
     else
         k_trace_batch<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dHitI, dHitT, (float4 *)dHits);
+    FLX_LAUNCHED(ctx);
+    return FLX_OK;
+}
+
+// CLContext::pickSingle (clcontext.cpp:934-949): one ray, one warp
+int flx_launch_pick(flx_ctx *ctx, float ndcX, float ndcY, flx_hit *dHit)
+{
+    FLX_CUDA(ctx, traceKernelSetup(ctx));
+    unsigned int *cur = workCursor(ctx, 1);
+    FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
+    k_pick<<<1, 32, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ndcX, ndcY, (float4 *)dHit, cur, ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }

@@ -121,6 +121,13 @@ void orc_wf_logic(void *h, int firstIteration) { ((Wavefront *)h)->logic(firstIt
 void orc_wf_materials(void *h) { ((Wavefront *)h)->materials(); }
 void orc_wf_ext(void *h) { ((Wavefront *)h)->extRays(); }
 void orc_wf_shadow(void *h) { ((Wavefront *)h)->shadowRays(); }
+void orc_wf_pick(void *h, float ndcX, float ndcY, flx_hit *out)
+{
+    const Hit hit = ((Wavefront *)h)->pick(ndcX, ndcY);
+    memset(out, 0, sizeof(*out));
+    out->P.x = hit.P.x; out->P.y = hit.P.y; out->P.z = hit.P.z; out->N.x = hit.N.x; out->N.y = hit.N.y; out->N.z = hit.N.z;
+    out->uvTex.x = hit.uv.x; out->uvTex.y = hit.uv.y; out->t = hit.t; out->i = hit.i; out->areaLightHit = hit.areaLightHit; out->matId = hit.matId;
+}
 void orc_mk_reset(void *h) { ((Wavefront *)h)->mkReset(); }
 void orc_mk_raygen(void *h) { ((Wavefront *)h)->mkRaygen(); }
 void orc_mk_next_vertex(void *h) { ((Wavefront *)h)->mkNextVertex(); }

@@ -207,6 +207,23 @@ void Wavefront::shadowRays()
     shadowCounters.tri_tests += acc.tri_tests; shadowCounters.hits += acc.hits;
 }
 
+// kernel_pick.cl:6-41 (CLContext::pickSingle): ray through an NDC point from the camera position, no lens sample
+Hit Wavefront::pick(float NDCx, float NDCy)
+{
+    float SCRx = NDCx + NDCx - 1.0f;
+    float SCRy = NDCy + NDCy - 1.0f;
+    SCRx *= (float)params.width * params.height1;
+    SCRx *= params.camera.fovSCALE;
+    SCRy *= params.camera.fovSCALE;
+    const f3 pos = ld3(params.camera.pos);
+    const f3 rayTarget = pos + ld3(params.camera.right) * SCRx + ld3(params.camera.up) * SCRy + ld3(params.camera.dir);
+    Ray r; r.orig = pos; r.dir = normalize(rayTarget - pos);
+    Hit hit = emptyHit(FLT_MAX);
+    if (useBitstack) bvhIntersectBitstack(r, &hit, geo, nullptr); else bvhIntersectStack(r, &hit, geo, nullptr);
+    if (params.sampleImpl && params.useAreaLight) intersectLight(&hit, r, &params);
+    return hit;
+}
+
 void Wavefront::clearQueues() { memset(&cnt, 0, sizeof(cnt)); } // clcontext.cpp:903-909
 
 void Wavefront::updatePixelIndex(uint32_t numNewPaths) // clcontext.cpp:917-921

@@ -43,6 +43,7 @@ struct Wavefront
     void clearQueues();                 // CLContext::enqueueClearWfQueues
     void postprocess(float *outRGBA);   // mk_postprocess.cl
     void updatePixelIndex(uint32_t numNewPaths); // CLContext::updatePixelIndex
+    Hit pick(float NDCx, float NDCy);   // kernel_pick.cl
 
     // microkernel renderer (o_microkernel.cpp): src/mk_*.cl, one task per pixel, phase word in slot 46
     flx_render_stats stats = {0, 0, 0, 0};  // device RenderStats (mk_next_vertex.cl:44-56, mk_sample_bsdf.cl:97,127, mk_splat.cl:39)

@@ -158,6 +158,13 @@ class OracleWavefront:
     def set_pixel_index(self, v): self.L.orc_wf_set_pixel_index(self.h, U32(int(v)))
     def get_pixel_index(self): return int(self.L.orc_wf_get_pixel_index(self.h))
 
+    def pick(self, ndc_x, ndc_y):
+        """kernel_pick.cl: the Hit under an NDC point (HIT_DT record)."""
+        from fluctus_b200.abi import HIT_DT
+        out = np.zeros(1, HIT_DT)
+        self.L.orc_wf_pick(self.h, C.c_float(ndc_x), C.c_float(ndc_y), _ptr(out))
+        return out[0]
+
     # microkernel renderer (src/mk_*.cl): one task per pixel, phase word in state slot 46
     def mk_reset(self): self.L.orc_mk_reset(self.h)
     def mk_raygen(self): self.L.orc_mk_raygen(self.h)

@@ -208,3 +208,27 @@ def test_cfg5_full_size_microbench_parity(oracle, teapot):
         assert not c.traceAny(miss).any()
     finally:
         c.close()
+
+
+def test_pick_single_matches_oracle(oracle, teapot):
+    """CLContext::pickSingle / kernel_pick.cl: the Hit record under NDC points, bit-exact, including the light quad
+    reported as an implicit hit (i = 0, matId = 0, areaLightHit = 1) when sampleImpl && useAreaLight."""
+    from fluctus_b200 import CudaContext, abi, scene as fs
+    W, H = 640, 360
+    for impl in (True, False):
+        p = abi.make_render_params(W, H, n_tris=len(teapot["tris"]), world_radius=fs.world_radius(teapot), use_env_map=False,
+                                   use_area_light=True, sample_implicit=impl, cam_pos=(0.0, 0.2, 1.6),
+                                   light_pos=(0.0, 0.9, 0.0), light_n=(0.0, 0.0, 1.0), light_right=(1.0, 0.0, 0.0), light_up=(0.0, 1.0, 0.0),
+                                   light_size=(0.6, 0.3))
+        wf = oracle.OracleWavefront(64, W, H)
+        wf.set_scene(teapot); wf.set_params(p.tobytes())
+        ctx = CudaContext(num_tasks=64)
+        ctx.uploadSceneData(teapot); ctx.updateParams(p)
+        kinds = set()
+        for y in np.linspace(0.02, 0.98, 13):
+            for x in np.linspace(0.02, 0.98, 17):
+                g, r = ctx.pickSingle(float(x), float(y)), wf.pick(float(x), float(y))
+                assert g.tobytes() == r.tobytes(), (x, y, g, r)
+                kinds.add("light" if r["areaLightHit"] else ("tri" if r["i"] >= 0 else "miss"))
+        assert kinds == ({"light", "tri", "miss"} if impl else {"tri", "miss"}), kinds
+        ctx.close()
