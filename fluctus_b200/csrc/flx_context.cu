@@ -18,6 +18,8 @@ int flx_fail(flx_ctx *ctx, int code, const std::string &msg)
 
 static void invalidateGraph(flx_ctx *ctx)
 {
+    // replays of the old graph may still be in flight on the stream: let them drain before the executable goes away
+    if ((ctx->graphExec || ctx->mkGraphExec) && ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->graphExec) { cudaGraphExecDestroy(ctx->graphExec); ctx->graphExec = nullptr; }
     ctx->graphValid = false;
     if (ctx->mkGraphExec) { cudaGraphExecDestroy(ctx->mkGraphExec); ctx->mkGraphExec = nullptr; }

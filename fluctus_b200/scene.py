@@ -190,3 +190,27 @@ def load_flxs(path):
             n = ew * eh
             env = dict(rgb=rd(np.float32, 3 * n).reshape(eh, ew, 3), prob=rd(np.float32, n), alias=rd(np.int32, n), pdf=rd(np.float32, n))
     return scene, env
+
+
+def build_lbvh(scene, max_leaf=4, device=0):
+    """Rebuild the hierarchy of `scene` on the GPU (flx_build_lbvh: Morton order + Karras' radix tree, emitted in the
+    reference's Node[] / index-list format).  Returns a copy of the scene with `nodes`, `indices`, `bounds` replaced
+    and `lbvh_depth` added; triangles, materials and textures are shared with the input."""
+    import ctypes as C
+    from ._lib import FluctusError, load
+    L = load()
+    tris = np.ascontiguousarray(scene["tris"], TRI_DT)
+    n = len(tris)
+    nodes = np.zeros(2 * n - 1, NODE_DT)
+    indices = np.zeros(n, np.uint32)
+    n_nodes, depth = C.c_size_t(0), C.c_uint32(0)
+    rc = L.flx_build_lbvh(int(device), tris.ctypes.data_as(C.c_void_p), n, int(max_leaf), nodes.ctypes.data_as(C.c_void_p),
+                          len(nodes), C.byref(n_nodes), indices.ctypes.data_as(C.c_void_p), C.byref(depth))
+    if rc != 0:
+        raise FluctusError("%s (flx_status %d)" % (L.flx_last_error(None).decode(), rc))
+    out = dict(scene)
+    out["nodes"] = nodes[:n_nodes.value].copy()
+    out["indices"] = indices
+    out["bounds"] = scene_bounds(out)
+    out["lbvh_depth"] = int(depth.value)
+    return out

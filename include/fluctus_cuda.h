@@ -132,6 +132,17 @@ int flx_read_pixels(flx_ctx *ctx, int which /* flx_buffer */, void *host_out, si
 void *flx_device_ptr(flx_ctx *ctx, int which /* flx_buffer */); /* for the per-frame all-reduce */
 int flx_pick(flx_ctx *ctx, float ndc_x, float ndc_y, flx_hit *out);
 
+/* ---- parallel hierarchy build (new) --------------------------------------------------------
+ * Linear BVH (63-bit Morton order + Karras' radix tree, subtrees of <= max_leaf triangles collapsed into one leaf)
+ * built on GPU `device` and returned in the reference's own format — Node[] in depth-first order with the left
+ * child at index + 1 (src/bvhnode.hpp:50-59) and the index list its leaves point into — i.e. a drop-in for the
+ * arrays BVH / SBVH (src/bvh.cpp, src/sbvh.cpp) hand to CLContext::uploadSceneData.  nodes_capacity >= 2*n_tris - 1
+ * always suffices; *n_nodes_out receives the number written; indices_out has n_tris entries; *depth_out (optional)
+ * the depth of the tree (flx_upload_scene refuses hierarchies deeper than its 64-entry traversal stack).
+ * Stateless and synchronous.  No CPU fallback. */
+int flx_build_lbvh(int device, const flx_triangle *tris, size_t n_tris, uint32_t max_leaf,
+                   flx_node *nodes_out, size_t nodes_capacity, size_t *n_nodes_out, uint32_t *indices_out, uint32_t *depth_out);
+
 /* ---- ray-cast entry points (parity + microbench; cover kernel_pick.cl as well) -------------------
  * rays: n x 8 floats (ox,oy,oz,tmax, dx,dy,dz,unused).  Host-buffer variants copy in, trace, copy
  * out and synchronise; *_device variants take device pointers and only enqueue. Any output may be NULL. */
