@@ -135,6 +135,20 @@ public:
 
     uint64_t launchCount() const { return flx_launch_count(ctx); }
 
+    // ---- hierarchy build on the GPU (new): stands in for BVH / SBVH construction (src/bvh.cpp, src/sbvh.cpp) -----
+    // Returns Node[] (depth-first, left child at index + 1) and fills `indices`: the arrays uploadSceneData takes.
+    static std::vector<flx_node> buildHierarchy(const flx_triangle *tris, size_t nTris, std::vector<uint32_t> &indices,
+                                                uint32_t maxLeaf = 4, int device = 0, uint32_t *depth = nullptr)
+    {
+        std::vector<flx_node> nodes(nTris ? 2 * nTris - 1 : 0);
+        indices.assign(nTris, 0u);
+        size_t nNodes = 0;
+        const int rc = flx_build_lbvh(device, tris, nTris, maxLeaf, nodes.data(), nodes.size(), &nNodes, indices.data(), depth);
+        if (rc != FLX_OK) throw std::runtime_error(std::string(flx_last_error(nullptr)) + " (flx_status " + std::to_string(rc) + ")");
+        nodes.resize(nNodes);
+        return nodes;
+    }
+
 private:
     void check(int rc) const
     {

@@ -7,7 +7,7 @@
 // the reference's batch mode does: the microkernel renderer, exactly SPP samples in every pixel, deterministic.
 //
 //   fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings settings.json] [--env map.hdr] [--bounces N]
-//                    [--renderer wavefront|mk] [--tasks N] [--iterations N] [--device D]
+//                    [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D]
 //                    [--out image.ppm|.pfm] [--save-scene out.flxs] scene...
 //
 // scene: a .flxs container (host_scene.hpp) or — when built against the reference tree — any file the
@@ -23,7 +23,7 @@
 static void usage()
 {
     std::cerr << "usage: fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings FILE] [--env FILE.hdr] [--bounces N]\n"
-                 "                        [--renderer wavefront|mk] [--tasks N] [--iterations N] [--device D]\n"
+                 "                        [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D]\n"
                  "                        [--out FILE.ppm|.pfm] [--save-scene FILE.flxs] scene...\n";
 }
 
@@ -33,7 +33,7 @@ int main(int argc, char **argv)
 {
     flx::Settings settings;
     int width = -1, height = -1, spp = 32, device = 0, bounces = -1;
-    uint32_t iterations = 0, tasks = 0;
+    uint32_t iterations = 0, tasks = 0, lbvhLeaf = 0;
     bool useMK = false;
     std::string out = "output.ppm", saveScene, env;
     std::vector<std::string> scenes;
@@ -55,6 +55,7 @@ int main(int argc, char **argv)
             else if (a == "--device") device = std::stoi(next());
             else if (a == "--renderer") { const std::string r = next(); if (r != "mk" && r != "wavefront") throw std::runtime_error("--renderer mk|wavefront"); useMK = (r == "mk"); }
             else if (a == "--tasks") tasks = (uint32_t)std::stoul(next());
+            else if (a == "--lbvh") lbvhLeaf = (uint32_t)std::stoul(next());
             else if (a == "--out") out = next();
             else if (a == "--save-scene") saveScene = next();
             else if (!a.empty() && a[0] == '-') throw std::runtime_error("unknown option " + a);
@@ -88,6 +89,12 @@ int main(int argc, char **argv)
 #else
                 throw std::runtime_error("this build reads .flxs scenes only (built without the reference tree); got " + scenes[si]);
 #endif
+            }
+            if (lbvhLeaf) // replace the hierarchy that came with the scene by one built on the GPU (flx_build_lbvh)
+            {
+                uint32_t depth = 0;
+                scene.nodes = flx::CudaContext::buildHierarchy(scene.tris.data(), scene.tris.size(), scene.indices, lbvhLeaf, device, &depth);
+                std::cerr << "rebuilt hierarchy on the GPU: " << scene.nodes.size() << " nodes, depth " << depth << "\n";
             }
             if (!saveScene.empty()) flx::saveScene(saveScene, scene);
 
