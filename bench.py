@@ -75,7 +75,8 @@ def config_dict(n_gpus, scene, impl):
             "step": "one frame: reset + iterations + all-reduce + tonemap" if impl == "ours"
                     else "steady-state wavefront iterations on the CPU path pool",
             "parallelism": "sample-sharded x%d, one all-reduce of the accumulation buffer per frame" % n_gpus,
-            "l2": "inputs larger than L2: 208 MB path state + 33 MB frame per pass (L2 126 MB)",
+            "l2": "inputs larger than L2: %d MB path state + 33 MB frame per pass (L2 126 MB), no flush needed"
+                  % ((NUM_TASKS if impl == "ours" else CPU_TASKS) * 212 // (1 << 20)),
             "stand_in_for": "assets/country_kitchen/Country-Kitchen.obj (stripped from the reference snapshot)"}
 
 
