@@ -1,0 +1,15 @@
+#!/bin/bash
+# The evidence run kept under profiles/ (run on the GPU box: gpurun -- 'bash tools/profile_round.sh r1f'):
+#   1. the full default bench line (never under a profiler),
+#   2. the ncu launch list of a short bench command (gpu__time_duration.sum only: shares, not absolutes),
+#   3. one `ncu --set full` capture of the traversal launch at a steady-state iteration.
+# Summaries: tools/ncu_summary.py launches|kernel, tools/ncu_lines.py.
+TAG=${1:-rX}
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || exit 1
+CMD="python bench.py --steps 2 --warmup 3 --no-raycast --no-cpu-baseline"
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launch.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_ext_shadow" --launch-skip 100 -c 1 -o gpurun_out/${TAG}_k_ext_shadow $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
+tail -2 gpurun_out/${TAG}_ncu_full.log
+cut -c1-400 gpurun_out/${TAG}_bench.json
