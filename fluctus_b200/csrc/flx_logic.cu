@@ -8,6 +8,9 @@
 #ifndef FLX_LOGIC_MIN_BLOCKS
 #define FLX_LOGIC_MIN_BLOCKS 4
 #endif
+#ifndef FLX_WF_GRID_PER_SM
+#define FLX_WF_GRID_PER_SM 64 // CTAs per SM in the grid of the logic / material kernels (tools/tune_defs.sh: 8 -> 64 is +2 %: finer-grained balance of divergent blocks)
+#endif
 #ifndef FLX_MAT_MIN_BLOCKS
 #define FLX_MAT_MIN_BLOCKS 4
 #endif
@@ -380,7 +383,7 @@ k_materials_separate(PathState st, Queues qs, uint32_t N, MaterialsDev md)
 static inline int wfGrid(const flx_ctx *ctx, uint64_t items)
 {
     const uint64_t blocks = (items + FLX_WF_THREADS - 1) / FLX_WF_THREADS;
-    const uint64_t cap = (uint64_t)ctx->numSMs * 8;
+    const uint64_t cap = (uint64_t)ctx->numSMs * FLX_WF_GRID_PER_SM;
     return (int)(blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
 }
 #define FLX_LAUNCHED(ctx) do { (ctx)->launches++; FLX_CUDA(ctx, cudaGetLastError()); } while (0)
