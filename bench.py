@@ -63,7 +63,7 @@ def load_workload():
     env = fs.load_envmap(os.path.join(GOLDEN, "night_env.npz"))
     scene, view = kitchen_standin(teapot)
     settings = dict(max_bounces=MAX_BOUNCES, use_env_map=True, use_area_light=True, sample_implicit=True,
-                    sample_explicit=True, use_roulette=False, separate_queues=True, tonemap=2, **view)
+                    sample_explicit=True, use_roulette=False, separate_queues=os.environ.get("FLX_BENCH_SEPARATE", "1") != "0", tonemap=2, **view)
     return teapot, scene, env, settings
 
 
