@@ -58,8 +58,9 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
 {
     const uint32_t numPixels = params.width * params.height;
     const uint32_t maxId = firstIteration ? min(numPixels, N) : N;
-    const uint32_t rounded = (maxId + 31u) & ~31u;
+    const uint32_t rounded = (maxId + FLX_WF_THREADS - 1u) & ~(uint32_t)(FLX_WF_THREADS - 1u); // whole CTAs: the push below has barriers
     const bool checkSpp = params.maxSpp > 0u; // -DCHECK_SPP
+    __shared__ uint32_t sPush[FLX_WF_THREADS / 32][16]; // per warp: slot counts, then slot bases, of the ten counters
     const bool separate = params.wfSeparateQueues != 0u;
     const uint32_t cursor = REGEN ? *currPixelIdx : 0u;
 
@@ -261,8 +262,24 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
             }
             const unsigned mSplat = checkSpp ? __ballot_sync(FULL, splatted) : 0u;
             if (lane == 9u) mine = mSplat;
-            uint32_t base = 0u;
-            if (mine != 0u) base = atomicAdd(((uint32_t *)qs.counters) + lane, (uint32_t)__popc(mine));
+            // CTA-level aggregation: the ten counters share one 32-byte sector, and the L2 atomic unit serialises the
+            // operations on it — one request per warp (131 k per launch at 2^22 paths) kept that unit busy for most of the
+            // kernel.  The eight warps of a CTA pool their counts in shared memory and warp 0 reserves for all of them.
+            const unsigned warp = threadIdx.x >> 5;
+            if (lane < 10u) sPush[warp][lane] = (uint32_t)__popc(mine);
+            __syncthreads();
+            if (warp == 0u && lane < 10u)
+            {
+                uint32_t total = 0u;
+#pragma unroll
+                for (int w = 0; w < FLX_WF_THREADS / 32; w++) { const uint32_t c = sPush[w][lane]; sPush[w][lane] = total; total += c; }
+                const uint32_t b = total ? atomicAdd(((uint32_t *)qs.counters) + lane, total) : 0u;
+#pragma unroll
+                for (int w = 0; w < FLX_WF_THREADS / 32; w++) sPush[w][lane] += b;
+            }
+            __syncthreads();
+            const uint32_t base = lane < 10u ? sPush[warp][lane] : 0u;
+            __syncwarp();
             const unsigned lt = (1u << lane) - 1u;
             // every lane asks the reserving lane of its queue for the base and the mask (two shuffles per push)
             const int srcA = myQ >= 0 ? myQ : 0;
