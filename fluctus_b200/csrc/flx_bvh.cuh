@@ -113,21 +113,22 @@ struct TravCount { unsigned int inner, leaf, tri; };
 //   * else the inner-node body.
 // Once a body is chosen the warp stays in it while >= FLX_STAY_* lanes still have work of that kind (one ballot
 // per pass instead of the full vote).  Lanes whose state was not chosen wait; they are picked up as soon as
-// enough peers join them.  Thresholds were tuned on B200 with tools/tune_vote.sh (kitchen render + cfg5 rays).
+// enough peers join them.  Thresholds were tuned on B200 with tools/tune_vote.sh (kitchen render + cfg5 rays); re-tuned
+// for the 2^22-path pool and the fused extension+shadow launch: 12/8/4/8 -> 16/6/3/12 is +7 % on the kitchen, cfg5 unchanged.
 // A Job supplies the rays and consumes the results:
 //     bool load(unsigned k, f3 &o, f3 &d, float &tmax)   // false: ray k needs no traversal (already resolved)
 //     void store(const RayHit &h, f3 o, f3 d)            // result of the ray loaded last by this lane
 #ifndef FLX_VOTE_RETIRE
-#define FLX_VOTE_RETIRE 12
+#define FLX_VOTE_RETIRE 16
 #endif
 #ifndef FLX_VOTE_LEAF
-#define FLX_VOTE_LEAF 8
+#define FLX_VOTE_LEAF 6
 #endif
 #ifndef FLX_STAY_LEAF
-#define FLX_STAY_LEAF 4
+#define FLX_STAY_LEAF 3
 #endif
 #ifndef FLX_STAY_INNER
-#define FLX_STAY_INNER 8
+#define FLX_STAY_INNER 12
 #endif
 #define FLX_TRAV_DONE ((int)0x80000000) // not a valid ref: leaf refs are ~slot with slot < 0x7fffffff
 
