@@ -46,10 +46,12 @@ struct ExtJob
 {
     const DevBVH &bvh; const PathState &st; const uint32_t *queue; const flx_render_params &params;
     uint32_t gid; unsigned int nHits, nRays;
+    uint32_t len; // pathLen, which travels in the .w lane of the direction: kept so that the store needs no read
     FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
     {
         gid = queue[k];
-        o = mk3(st.ray0[gid]); d = mk3(st.ray1[gid]); tmax = FLX_FLT_MAX;
+        const float4 r1 = st.ray1[gid];
+        o = mk3(st.ray0[gid]); d = mk3(r1); len = __float_as_uint(r1.w); tmax = FLX_FLT_MAX;
         return true;
     }
     FLX_DEV void store(const RayHit &h, f3 o, f3 d)
@@ -71,8 +73,7 @@ struct ExtJob
         st.hit0[gid] = mk4(P, t);
         st.hit1[gid] = mk4i(N, hi);
         st.hit2[gid] = make_float4(uvx, uvy, __int_as_float(matId), __int_as_float(al));
-        uint32_t *len = reinterpret_cast<uint32_t *>(&st.ray1[gid].w);
-        *len = *len + 1u; // pathLen += 1
+        st.ray1[gid].w = __uint_as_float(len + 1u); // pathLen += 1
     }
 };
 
@@ -111,7 +112,8 @@ struct MkVertexJob
     {
         if (ext.st.phase[k] != FLX_MK_RT_NEXT_VERTEX) return false;
         ext.gid = k;
-        o = mk3(ext.st.ray0[k]); d = mk3(ext.st.ray1[k]); tmax = FLX_FLT_MAX;
+        const float4 r1 = ext.st.ray1[k];
+        o = mk3(ext.st.ray0[k]); d = mk3(r1); ext.len = __float_as_uint(r1.w); tmax = FLX_FLT_MAX;
         return true;
     }
     FLX_DEV void store(const RayHit &h, f3 o, f3 d) { ext.store(h, o, d); }
@@ -241,7 +243,7 @@ k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_qu
     const unsigned int total = counters->extensionQueue;
     if (total == 0u) return;
     stageTopNodes(bvh, topNodes);
-    ExtJob job = {bvh, st, queue, params, 0u, 0u, 0u};
+    ExtJob job = {bvh, st, queue, params, 0u, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
     traceLoop<false, COUNT>(bvh, topNodes, job, cursor, total, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
@@ -279,7 +281,7 @@ k_ext_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ extQueue, co
         TravCount cnt = {0u, 0u, 0u};
         if (nExt)
         {
-            ExtJob job = {bvh, st, extQueue, params, 0u, 0u, 0u};
+            ExtJob job = {bvh, st, extQueue, params, 0u, 0u, 0u, 0u};
             traceLoop<false, false>(bvh, topNodes, job, cursors, nExt, cnt);
         }
         if (nShadow)
@@ -308,7 +310,7 @@ k_mk_vertex(DevBVH bvh, PathState st, unsigned int total, unsigned int *cursor, 
 {
     extern __shared__ float4 topNodes[];
     stageTopNodes(bvh, topNodes);
-    MkVertexJob job = {{bvh, st, nullptr, params, 0u, 0u, 0u}};
+    MkVertexJob job = {{bvh, st, nullptr, params, 0u, 0u, 0u, 0u}};
     TravCount cnt = {0u, 0u, 0u};
     traceLoop<false, false>(bvh, topNodes, job, cursor, total, cnt);
 }
