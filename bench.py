@@ -226,10 +226,11 @@ def recorded_traffic():
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         if int(t.get("num_tasks", 0)) == NUM_TASKS:
-            return t["dram_bytes_per_launch"] / 1e9, t["source"]
+            extra = {k: t[k] for k in ("issue_slots_busy_pct", "lanes_per_instruction", "l1_hit_pct", "l2_hit_pct") if k in t}
+            return t["dram_bytes_per_launch"] / 1e9, t["source"], extra
     except (OSError, ValueError, KeyError):
         pass
-    return None, None
+    return None, None, {}
 
 
 def traversal_bytes(cnt, rays=None, any_hit=False):
@@ -429,7 +430,7 @@ def run_ours(args):
     trace_achieved = (ext_bytes + shw_bytes) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
     stage_ms = {("trace" if k == "ext" else k): s[0] for k, s in r["stage"].items() if k not in ("shadow", "raygen") or s[0] > 0}
     stage_sum = sum(stage_ms.values())
-    traffic_gb, traffic_src = recorded_traffic()
+    traffic_gb, traffic_src, traffic_extra = recorded_traffic()
 
     raycast = None
     if not args.no_raycast:
@@ -452,10 +453,11 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "kernel": "k_ext_shadow (extension closest-hit + shadow any-hit traversal of one iteration, one persistent launch)",
                          "achieved": trace_achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                          "frac": trace_achieved / peak, "traffic": traffic_gb, "traffic_unit": "GB per launch (DRAM read + write)",
-                         "traffic_source": traffic_src,
+                         "traffic_source": traffic_src, "ncu": traffic_extra,
                          "algorithmic_gb_per_launch": (ext_bytes + shw_bytes) / max(ext_n, 1) / 1e9,
                          "note": "the tree of this scene (37 MB) is served from L1/L2: DRAM traffic is a fraction of the algorithmic "
-                                 "bytes and the kernel is bound by instruction issue, not by HBM (profiles/r1f_k_ext_shadow_full.md)",
+                                 "bytes (so achieved can exceed the HBM peak) and the kernel is bound by instruction issue, not by HBM "
+                                 "(profiles/r1i_k_ext_shadow_full.md)",
                          "launches": int(ext_n), "avg_launch_ms": ext_ms / max(ext_n, 1),
                          "algorithmic_bytes_per_ray": {"extension": ext_per_ray, "shadow": shw_per_ray},
                          "rays_per_launch": {"extension": r["local"]["extension"] / max(ext_n, 1), "shadow": r["local"]["shadow"] / max(ext_n, 1)},
