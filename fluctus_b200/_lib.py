@@ -39,6 +39,7 @@ SIGNATURES = {
     "flx_finish": (I32, [V]),
     "flx_render": (I32, [V, U32, I32]),
     "flx_build_lbvh": (I32, [I32, V, SZ, U32, V, SZ, V, V, V]),
+    "flx_reduce_frames": (I32, [V, I32]),
     "flx_mk_reset": (I32, [V]),
     "flx_mk_raygen": (I32, [V]),
     "flx_mk_next_vertex": (I32, [V]),

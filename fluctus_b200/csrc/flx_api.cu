@@ -1,6 +1,7 @@
 // C-ABI, second half: stage dispatch, the graph-replayed render loop, read-back, ray-cast entry
 // points, state inspection.  See include/fluctus_cuda.h for the reference method each one replaces.
 #include "flx_internal.h"
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 
@@ -274,22 +275,79 @@ int flx_trace_any_device(flx_ctx *ctx, const void *d_rays, size_t n, void *d_occ
     return flx_launch_any_batch(ctx, (const float4 *)d_rays, n, (uint8_t *)d_occluded);
 }
 
+// Host-buffer ray casts are PCIe-bound: 32 B up and 8 B (+64 B with full hit records) down per ray against ~0.4 ns of
+// traversal.  The batch is cut into chunks of FLX_RAY_CHUNK rays: chunk c+1 is uploaded on `copyIn` while chunk c is
+// traversed on the context's stream and chunk c-1 is downloaded on `copyOut` (both copy engines and the SMs busy at
+// the same time), so the call costs about max(upload, traversal, download) instead of their sum.
+#ifndef FLX_RAY_CHUNK
+#define FLX_RAY_CHUNK (1u << 20)
+#endif
+namespace {
+struct RayPipe
+{
+    flx_ctx *ctx; size_t nChunks;
+    int init(flx_ctx *c, size_t n)
+    {
+        ctx = c; nChunks = (n + FLX_RAY_CHUNK - 1) / FLX_RAY_CHUNK;
+        if (!ctx->copyIn) FLX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copyIn, cudaStreamNonBlocking));
+        if (!ctx->copyOut) FLX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copyOut, cudaStreamNonBlocking));
+        while (ctx->pipeEvents.size() < 2 * nChunks + 1)
+        {
+            cudaEvent_t e; FLX_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            ctx->pipeEvents.push_back(e);
+        }
+        // the copy streams start behind whatever is already queued on the context's stream (scratch reuse)
+        cudaEvent_t start = ctx->pipeEvents[2 * nChunks];
+        FLX_CUDA(ctx, cudaEventRecord(start, ctx->stream));
+        FLX_CUDA(ctx, cudaStreamWaitEvent(ctx->copyIn, start, 0));
+        FLX_CUDA(ctx, cudaStreamWaitEvent(ctx->copyOut, start, 0));
+        return FLX_OK;
+    }
+    int uploaded(size_t c) // chunk c is on the device: the context's stream may traverse it
+    {
+        FLX_CUDA(ctx, cudaEventRecord(ctx->pipeEvents[2 * c], ctx->copyIn));
+        FLX_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipeEvents[2 * c], 0));
+        return FLX_OK;
+    }
+    int traced(size_t c) // results of chunk c are ready: the download stream may fetch them
+    {
+        FLX_CUDA(ctx, cudaEventRecord(ctx->pipeEvents[2 * c + 1], ctx->stream));
+        FLX_CUDA(ctx, cudaStreamWaitEvent(ctx->copyOut, ctx->pipeEvents[2 * c + 1], 0));
+        return FLX_OK;
+    }
+    int finish()
+    {
+        FLX_CUDA(ctx, cudaStreamSynchronize(ctx->copyOut));
+        return flx_finish(ctx);
+    }
+};
+} // namespace
+
 int flx_trace_closest(flx_ctx *ctx, const float *rays, size_t n, int32_t *hit_i, float *hit_t, flx_hit *hits)
 {
     FLX_CHECK_CTX(ctx); FLX_CUDA(ctx, cudaSetDevice(ctx->device));
     if (n == 0) return FLX_OK;
     if (!rays) return flx_fail(ctx, FLX_ERR_ARG, "flx_trace_closest: null rays");
-    const size_t rayBytes = n * 32, iBytes = n * 4, hBytes = hits ? n * sizeof(flx_hit) : 0;
+    if (!ctx->sceneReady) return flx_fail(ctx, FLX_ERR_STATE, "scene not uploaded (flx_upload_scene)");
+    // sub-buffers on 256-byte boundaries: the hit records are written as float4 whatever the parity of n
+    const size_t rayBytes = n * 32, iBytes = (n * 4 + 255) & ~(size_t)255, hBytes = hits ? n * sizeof(flx_hit) : 0;
     FLX_TRY(ensureScratch(ctx, rayBytes + 2 * iBytes + hBytes));
     uint8_t *base = (uint8_t *)ctx->dScratch;
     float4 *dRays = (float4 *)base; int32_t *dI = (int32_t *)(base + rayBytes); float *dT = (float *)(base + rayBytes + iBytes);
     flx_hit *dH = hits ? (flx_hit *)(base + rayBytes + 2 * iBytes) : nullptr;
-    FLX_CUDA(ctx, cudaMemcpyAsync(dRays, rays, rayBytes, cudaMemcpyHostToDevice, ctx->stream));
-    FLX_TRY(flx_trace_closest_device(ctx, dRays, n, dI, dT, dH));
-    if (hit_i) FLX_CUDA(ctx, cudaMemcpyAsync(hit_i, dI, iBytes, cudaMemcpyDeviceToHost, ctx->stream));
-    if (hit_t) FLX_CUDA(ctx, cudaMemcpyAsync(hit_t, dT, iBytes, cudaMemcpyDeviceToHost, ctx->stream));
-    if (hits) FLX_CUDA(ctx, cudaMemcpyAsync(hits, dH, hBytes, cudaMemcpyDeviceToHost, ctx->stream));
-    return flx_finish(ctx);
+    RayPipe pipe; FLX_TRY(pipe.init(ctx, n));
+    for (size_t c = 0; c < pipe.nChunks; c++)
+    {
+        const size_t k0 = c * (size_t)FLX_RAY_CHUNK, m = std::min((size_t)FLX_RAY_CHUNK, n - k0);
+        FLX_CUDA(ctx, cudaMemcpyAsync(dRays + 2 * k0, rays + 8 * k0, m * 32, cudaMemcpyHostToDevice, ctx->copyIn));
+        FLX_TRY(pipe.uploaded(c));
+        FLX_TRY(flx_trace_closest_device(ctx, dRays + 2 * k0, m, dI + k0, dT + k0, dH ? dH + k0 : nullptr));
+        FLX_TRY(pipe.traced(c));
+        if (hit_i) FLX_CUDA(ctx, cudaMemcpyAsync(hit_i + k0, dI + k0, m * 4, cudaMemcpyDeviceToHost, ctx->copyOut));
+        if (hit_t) FLX_CUDA(ctx, cudaMemcpyAsync(hit_t + k0, dT + k0, m * 4, cudaMemcpyDeviceToHost, ctx->copyOut));
+        if (hits) FLX_CUDA(ctx, cudaMemcpyAsync(hits + k0, dH + k0, m * sizeof(flx_hit), cudaMemcpyDeviceToHost, ctx->copyOut));
+    }
+    return pipe.finish();
 }
 
 int flx_trace_any(flx_ctx *ctx, const float *rays, size_t n, uint8_t *occluded)
@@ -297,13 +355,21 @@ int flx_trace_any(flx_ctx *ctx, const float *rays, size_t n, uint8_t *occluded)
     FLX_CHECK_CTX(ctx); FLX_CUDA(ctx, cudaSetDevice(ctx->device));
     if (n == 0) return FLX_OK;
     if (!rays || !occluded) return flx_fail(ctx, FLX_ERR_ARG, "flx_trace_any: null argument");
+    if (!ctx->sceneReady) return flx_fail(ctx, FLX_ERR_STATE, "scene not uploaded (flx_upload_scene)");
     const size_t rayBytes = n * 32;
     FLX_TRY(ensureScratch(ctx, rayBytes + n));
-    uint8_t *base = (uint8_t *)ctx->dScratch;
-    FLX_CUDA(ctx, cudaMemcpyAsync(base, rays, rayBytes, cudaMemcpyHostToDevice, ctx->stream));
-    FLX_TRY(flx_trace_any_device(ctx, base, n, base + rayBytes));
-    FLX_CUDA(ctx, cudaMemcpyAsync(occluded, base + rayBytes, n, cudaMemcpyDeviceToHost, ctx->stream));
-    return flx_finish(ctx);
+    uint8_t *base = (uint8_t *)ctx->dScratch, *dOcc = base + rayBytes;
+    RayPipe pipe; FLX_TRY(pipe.init(ctx, n));
+    for (size_t c = 0; c < pipe.nChunks; c++)
+    {
+        const size_t k0 = c * (size_t)FLX_RAY_CHUNK, m = std::min((size_t)FLX_RAY_CHUNK, n - k0);
+        FLX_CUDA(ctx, cudaMemcpyAsync(base + 32 * k0, rays + 8 * k0, m * 32, cudaMemcpyHostToDevice, ctx->copyIn));
+        FLX_TRY(pipe.uploaded(c));
+        FLX_TRY(flx_trace_any_device(ctx, base + 32 * k0, m, dOcc + k0));
+        FLX_TRY(pipe.traced(c));
+        FLX_CUDA(ctx, cudaMemcpyAsync(occluded + k0, dOcc + k0, m, cudaMemcpyDeviceToHost, ctx->copyOut));
+    }
+    return pipe.finish();
 }
 
 // CLContext::pickSingle (clcontext.cpp:934-949) + kernel_pick.cl: one primary ray through the

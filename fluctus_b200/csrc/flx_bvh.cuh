@@ -132,15 +132,24 @@ struct TravCount { unsigned int inner, leaf, tri; };
 #endif
 #define FLX_TRAV_DONE ((int)0x80000000) // not a valid ref: leaf refs are ~slot with slot < 0x7fffffff
 
-// Hint the line holding the next node / leaf slot into L1 as soon as its address is known: the lane usually
-// waits at least one vote before it touches it.  No registers are held, and a wrong guess costs nothing.
+// Prefetch hints (experiment switches): FLX_PF_CUR covers the record a lane steps to next (it
+// usually waits at least one vote before touching it), FLX_PF_PUSH the record of a postponed far child — the reference
+// never re-tests a node on pop (src/bvh.cl:246-309), so for closest-hit rays every pushed node IS visited later and
+// the hint is never wasted.  0 = off, 1 = prefetch.global.L2, 2 = prefetch.global.L1.  No registers are held.
+#ifndef FLX_PF_CUR
+#define FLX_PF_CUR 0
+#endif
+#ifndef FLX_PF_PUSH
+#define FLX_PF_PUSH 0
+#endif
+template <int LEVEL>
 FLX_DEV void prefetchRef(const DevBVH &bvh, int ref)
 {
-#ifdef FLX_TRAV_PREFETCH
-    if (ref == FLX_TRAV_DONE) return;
+    if (LEVEL == 0) return;
+    if (ref == FLX_TRAV_DONE || (ref >= 0 && ref < bvh.topN)) return; // nothing to fetch / staged in shared memory
     const void *p = ref >= 0 ? (const void *)(bvh.nodes + 4 * (size_t)ref) : (const void *)(bvh.slots + 3 * (size_t)(~ref));
-    asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
-#endif
+    if (LEVEL == 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+    else asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 }
 
 template <bool ANY, bool COUNT, class Job>
@@ -217,7 +226,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                     if (ANY && found) cur = FLX_TRAV_DONE;
                     else if (__float_as_int(q1.w) != 0) cur = sp ? stack[--sp] : FLX_TRAV_DONE; // last slot of the leaf
                     else cur = cur - 1;                                                         // ~(slot + 1)
-                    prefetchRef(bvh, cur);
+                    prefetchRef<FLX_PF_CUR>(bvh, cur);
                 }
                 m = __ballot_sync(FULL, active && cur < 0 && cur != FLX_TRAV_DONE);
             } while (__popc(m) >= FLX_STAY_LEAF);
@@ -248,14 +257,16 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                     if (lh && rh)
                     {
                         const bool swap = rnear < lnear; // left first on equal entry distance (src/bvh.cl:293-300)
-                        stack[sp++] = swap ? l : r;
+                        const int far = swap ? l : r;
+                        stack[sp++] = far;
                         cur = swap ? r : l;
+                        if (!ANY) prefetchRef<FLX_PF_PUSH>(bvh, far);
                     }
                     else if (lh) cur = l;
                     else if (rh) cur = r;
                     else cur = sp ? stack[--sp] : FLX_TRAV_DONE;
                     if (COUNT && cur < 0 && cur != FLX_TRAV_DONE) cnt.leaf++;
-                    prefetchRef(bvh, cur);
+                    prefetchRef<FLX_PF_CUR>(bvh, cur);
                 }
                 m = __ballot_sync(FULL, active && cur >= 0);
             } while (__popc(m) >= FLX_STAY_INNER);

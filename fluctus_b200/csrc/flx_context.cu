@@ -120,6 +120,9 @@ void flx_destroy(flx_ctx *ctx)
     cudaFree(ctx->dEnv); cudaFree(ctx->dProb); cudaFree(ctx->dPdf); cudaFree(ctx->dAlias);
     cudaFree(ctx->stateBlock); cudaFree(ctx->queueBlock); cudaFree(ctx->fbBlock); cudaFree(ctx->dScratch);
     if (ctx->hCounters) cudaFreeHost(ctx->hCounters);
+    for (cudaEvent_t e : ctx->pipeEvents) cudaEventDestroy(e);
+    if (ctx->copyIn) cudaStreamDestroy(ctx->copyIn);
+    if (ctx->copyOut) cudaStreamDestroy(ctx->copyOut);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -141,8 +141,11 @@ struct flx_ctx
     // x {inner, leaf, tri, hits, rays}
     bool counting = false; unsigned long long *dTraceStats = nullptr;
 
-    // scratch for the host-buffer ray-cast entry points
+    // scratch for the host-buffer ray-cast entry points; two copy streams + one event pair per chunk so that the
+    // upload of chunk c+1, the traversal of chunk c and the download of chunk c-1 overlap (flx_api.cu: RayPipe)
     void *dScratch = nullptr; size_t scratchBytes = 0;
+    cudaStream_t copyIn = nullptr, copyOut = nullptr;
+    std::vector<cudaEvent_t> pipeEvents;
 };
 
 // error helpers -----------------------------------------------------------------------------------

@@ -127,6 +127,7 @@ public:
         check(flx_read_pixels(ctx, which, px.data(), px.size() * sizeof(float)));
         return px;
     }
+    void writePixels(int which, const std::vector<float> &px) { check(flx_write_pixels(ctx, which, px.data(), px.size() * sizeof(float))); }
     void *devicePtr(int which = FLX_BUF_PIXELS) { return flx_device_ptr(ctx, which); }
 
     // ---- ray casting -------------------------------------------------------------------------------
@@ -134,6 +135,21 @@ public:
     void traceAny(const float *rays8, size_t n, uint8_t *occluded) { check(flx_trace_any(ctx, rays8, n, occluded)); }
 
     uint64_t launchCount() const { return flx_launch_count(ctx); }
+
+    // ---- multi-GPU (new; the reference is single-device): contexts on different GPUs rendered sample shards of one
+    // frame; afterwards contexts[0] holds the summed accumulation buffer and the others are zero (flx_reduce_frames)
+    static void reduceFrames(const std::vector<CudaContext *> &contexts)
+    {
+        std::vector<flx_ctx *> h;
+        for (CudaContext *c : contexts) h.push_back(c->ctx);
+        if (flx_reduce_frames(h.data(), (int)h.size()) != FLX_OK)
+        {
+            std::string msg;
+            for (flx_ctx *c : h) { const char *m = flx_last_error(c); if (m && *m) { msg = m; break; } }
+            if (msg.empty()) msg = flx_last_error(nullptr);
+            throw std::runtime_error(msg);
+        }
+    }
 
     // ---- hierarchy build on the GPU (new): stands in for BVH / SBVH construction (src/bvh.cpp, src/sbvh.cpp) -----
     // Returns Node[] (depth-first, left child at index + 1) and fills `indices`: the arrays uploadSceneData takes.

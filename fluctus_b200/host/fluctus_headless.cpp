@@ -7,8 +7,19 @@
 // the reference's batch mode does: the microkernel renderer, exactly SPP samples in every pixel, deterministic.
 //
 //   fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings settings.json] [--env map.hdr] [--bounces N]
-//                    [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D]
+//                    [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D] [--gpus G]
+//                    [--benchmark SECONDS [--csv report.csv]] [--load-state F.dat] [--save-state F.dat]
+//                    [--load-accum F.flxa] [--save-accum F.flxa]
 //                    [--out image.ppm|.pfm] [--save-scene out.flxs] scene...
+//
+// --gpus G      sample-sharded render on devices D..D+G-1 from this one process (one HeadlessTracer and one host
+//               thread per GPU, seeds offset per rank, spp split); the accumulation buffers are summed over NVLink
+//               peer memory (flx_reduce_frames) and rank 0 writes the image.
+// --benchmark S Tracer::runBenchmark's timed loop (src/tracer.cpp:391-565) for S seconds per scene (the reference:
+//               30 s at 1024x1024): CSV rows `scene;time;primary;extension;shadow;total;samples` every half second
+//               to --csv, and the reference's one-line summary per scene on stdout.
+// --load-state / --save-state  the reference's data/states/state_<hash>.dat (camera, lights, sampling, tonemap).
+// --load-accum / --save-accum  raw accumulation checkpoint: a progressive render resumes where it stopped.
 //
 // scene: a .flxs container (host_scene.hpp) or — when built against the reference tree — any file the
 // reference's Scene::loadModel understands (.obj .ply .pbrt .pbf .sc.json), loaded and SBVH-built by the
@@ -18,12 +29,16 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <memory>
+#include <thread>
 #include "headless_tracer.hpp"
 
 static void usage()
 {
     std::cerr << "usage: fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings FILE] [--env FILE.hdr] [--bounces N]\n"
-                 "                        [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D]\n"
+                 "                        [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D] [--gpus G]\n"
+                 "                        [--benchmark SECONDS [--csv FILE.csv]] [--load-state F.dat] [--save-state F.dat]\n"
+                 "                        [--load-accum F.flxa] [--save-accum F.flxa]\n"
                  "                        [--out FILE.ppm|.pfm] [--save-scene FILE.flxs] scene...\n";
 }
 
@@ -32,10 +47,11 @@ static bool endsWith(const std::string &s, const std::string &e) { return s.size
 int main(int argc, char **argv)
 {
     flx::Settings settings;
-    int width = -1, height = -1, spp = 32, device = 0, bounces = -1;
+    int width = -1, height = -1, spp = 32, device = 0, bounces = -1, gpus = 1;
     uint32_t iterations = 0, tasks = 0, lbvhLeaf = 0;
     bool useMK = false;
-    std::string out = "output.ppm", saveScene, env;
+    double benchSeconds = 0.0;
+    std::string out = "output.ppm", saveScene, env, csvFile, loadState, saveState, loadAccum, saveAccum;
     std::vector<std::string> scenes;
     try
     {
@@ -56,6 +72,13 @@ int main(int argc, char **argv)
             else if (a == "--renderer") { const std::string r = next(); if (r != "mk" && r != "wavefront") throw std::runtime_error("--renderer mk|wavefront"); useMK = (r == "mk"); }
             else if (a == "--tasks") tasks = (uint32_t)std::stoul(next());
             else if (a == "--lbvh") lbvhLeaf = (uint32_t)std::stoul(next());
+            else if (a == "--gpus") gpus = std::stoi(next());
+            else if (a == "--benchmark") benchSeconds = std::stod(next());
+            else if (a == "--csv") csvFile = next();
+            else if (a == "--load-state") loadState = next();
+            else if (a == "--save-state") saveState = next();
+            else if (a == "--load-accum") loadAccum = next();
+            else if (a == "--save-accum") saveAccum = next();
             else if (a == "--out") out = next();
             else if (a == "--save-scene") saveScene = next();
             else if (!a.empty() && a[0] == '-') throw std::runtime_error("unknown option " + a);
@@ -65,6 +88,9 @@ int main(int argc, char **argv)
         if (width < 0) width = settings.windowWidth;
         if (height < 0) height = settings.windowHeight;
         if (width <= 0 || height <= 0 || spp < 0) throw std::runtime_error("invalid width / height / samples");
+        if (gpus < 1 || gpus > 16) throw std::runtime_error("--gpus 1..16");
+        if (benchSeconds < 0.0) throw std::runtime_error("--benchmark needs a positive duration");
+        if (gpus > 1 && (benchSeconds > 0.0 || !loadAccum.empty())) throw std::runtime_error("--benchmark / --load-accum run on one GPU");
         if (bounces >= 0) settings.maxPathDepth = bounces;
         if (env.empty()) env = settings.envMapName;
     }
@@ -103,27 +129,89 @@ int main(int argc, char **argv)
             if (tasks) sceneSettings.wfBufferSize = tasks;
             // the microkernel renderer keeps one task per pixel (mk_raygen.cl:8-9)
             if (useMK && (uint64_t)sceneSettings.wfBufferSize < (uint64_t)width * height) sceneSettings.wfBufferSize = (uint32_t)(width * height);
-            flx::HeadlessTracer tracer(width, height, sceneSettings, device);
-            tracer.init(scene);
+            // one tracer per GPU: rank r renders the samples of shard r (seed offset r*N, pixel cursor r*w*h/G, spp/G)
+            if (gpus > 1 && sceneSettings.maxSpp > 0) sceneSettings.maxSpp = (sceneSettings.maxSpp + gpus - 1) / gpus;
+            std::vector<std::unique_ptr<flx::HeadlessTracer>> tracers;
+            for (int r = 0; r < gpus; r++) tracers.emplace_back(new flx::HeadlessTracer(width, height, sceneSettings, device + r, r, gpus));
+            flx::HeadlessTracer &tracer = *tracers[0];
+            for (auto &t : tracers) { t->init(scene); if (!loadState.empty()) t->loadState(loadState); }
+            if (!saveState.empty()) tracer.saveState(saveState);
             const auto t0 = std::chrono::steady_clock::now();
             flx::CudaContext::Totals t{};
-            if (useMK) // Tracer::renderSingle — what the reference's own `-b -s SPP` runs (src/main.cpp, tracer.cpp:108-182)
+            if (benchSeconds > 0.0) // Tracer::runBenchmark
             {
-                const flx::RenderStats st = tracer.renderSingle((uint32_t)spp);
-                t.primary = st.primaryRays; t.extension = st.extensionRays; t.shadow = st.shadowRays; t.samples = st.samples;
-                t.iterations = (uint64_t)spp;
+                std::ofstream csv;
+                if (!csvFile.empty())
+                {
+                    csv.open(csvFile, si == 0 ? std::ios::out : std::ios::app);
+                    if (!csv) throw std::runtime_error("cannot write " + csvFile);
+                    if (si == 0) csv << "scene;time;primary;extension;shadow;total;samples\n";
+                }
+                std::ostringstream sink;
+                std::cout << tracer.runBenchmark(scenes[si], benchSeconds, csvFile.empty() ? (std::ostream &)sink : (std::ostream &)csv) << std::endl;
+                t = tracer.getClContext().getRenderTotals();
             }
-            else t = tracer.render((uint32_t)spp, iterations ? iterations : (1u << 20));
+            else
+            {
+                std::vector<flx::CudaContext::Totals> per(gpus);
+                std::vector<std::string> errors(gpus);
+                auto work = [&](int r)
+                {
+                    try
+                    {
+                        flx::HeadlessTracer &tr = *tracers[r];
+                        if (useMK) // Tracer::renderSingle — what the reference's own `-b -s SPP` runs (src/main.cpp, tracer.cpp:108-182)
+                        {
+                            const flx::RenderStats st = tr.renderSingle((uint32_t)spp); // takes this rank's share of spp itself
+                            per[r] = flx::CudaContext::Totals{st.primaryRays, st.extensionRays, st.shadowRays, st.samples, 0, (uint64_t)spp};
+                        }
+                        else
+                        {
+                            const uint32_t share = (uint32_t)spp / (uint32_t)gpus + ((uint32_t)r < (uint32_t)spp % (uint32_t)gpus ? 1u : 0u);
+                            if (!loadAccum.empty())
+                            {
+                                tr.render(0, 0); // reset + priming segment, then the checkpoint goes on top
+                                tr.loadAccumulation(loadAccum);
+                                per[r] = tr.resume(share, iterations ? iterations : (1u << 20));
+                            }
+                            else per[r] = tr.render(share, iterations ? iterations : (1u << 20));
+                        }
+                    }
+                    catch (const std::exception &e) { errors[r] = e.what(); }
+                };
+                if (gpus == 1) work(0);
+                else
+                {
+                    std::vector<std::thread> threads;
+                    for (int r = 0; r < gpus; r++) threads.emplace_back(work, r);
+                    for (auto &th : threads) th.join();
+                }
+                for (int r = 0; r < gpus; r++) if (!errors[r].empty()) throw std::runtime_error("GPU " + std::to_string(device + r) + ": " + errors[r]);
+                for (int r = 0; r < gpus; r++)
+                {
+                    t.primary += per[r].primary; t.extension += per[r].extension; t.shadow += per[r].shadow; t.samples += per[r].samples;
+                    t.splatted += per[r].splatted; t.iterations = std::max(t.iterations, per[r].iterations);
+                }
+                if (gpus > 1) // the frame = sum of the shards' accumulation buffers, left in rank 0's context
+                {
+                    std::vector<flx::CudaContext *> ctxs;
+                    for (auto &tr : tracers) ctxs.push_back(&tr->getClContext());
+                    flx::CudaContext::reduceFrames(ctxs);
+                }
+            }
+            if (!saveAccum.empty()) tracer.saveAccumulation(saveAccum);
             const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
             std::string file = out;
             if (scenes.size() > 1) file = out.substr(0, out.rfind('.')) + "_" + std::to_string(si) + out.substr(out.rfind('.'));
             tracer.saveImage(file);
+            uint64_t launches = 0;
+            for (auto &tr : tracers) launches += tr->getClContext().launchCount();
             printf("{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"triangles\": %zu, \"iterations\": %llu, \"primary\": %llu, "
                    "\"extension\": %llu, \"shadow\": %llu, \"samples\": %llu, \"seconds\": %.4f, \"msamples_per_s\": %.3f, "
-                   "\"mrays_per_s\": %.3f, \"kernel_launches\": %llu, \"image\": \"%s\"}\n",
+                   "\"mrays_per_s\": %.3f, \"gpus\": %d, \"kernel_launches\": %llu, \"image\": \"%s\"}\n",
                    scenes[si].c_str(), width, height, scene.tris.size(), (unsigned long long)t.iterations, (unsigned long long)t.primary,
                    (unsigned long long)t.extension, (unsigned long long)t.shadow, (unsigned long long)t.samples, sec, t.samples / sec * 1e-6,
-                   (t.primary + t.extension + t.shadow) / sec * 1e-6, (unsigned long long)tracer.getClContext().launchCount(), file.c_str());
+                   (t.primary + t.extension + t.shadow) / sec * 1e-6, gpus, (unsigned long long)launches, file.c_str());
         }
         catch (const std::exception &e)
         {

@@ -5,6 +5,7 @@
 // export arithmetic (CLContext::saveImage, src/clcontext.cpp:404-483).  The device side is CudaContext.
 #pragma once
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <fstream>
@@ -202,6 +203,12 @@ public:
         clctx.setPixelIndex(0);
         clctx.render(0, true);
         clctx.setPixelIndex(cursorStart());
+        if (maxIterations == 0) { clctx.finishQueue(); return clctx.getRenderTotals(); } // reset + priming segment only
+        return resume(spp, maxIterations, batch);
+    }
+    // continue an already reset renderer (after render(), loadAccumulation(), or a previous resume())
+    CudaContext::Totals resume(uint32_t spp, uint32_t maxIterations = 1u << 20, uint32_t batch = 16)
+    {
         const uint64_t target = (uint64_t)spp * params.width * params.height;
         CudaContext::Totals t{};
         for (uint32_t done = 0; done < maxIterations; done += batch)
@@ -229,6 +236,82 @@ public:
         clctx.enqueuePostprocessKernel(params);
         clctx.fetchStats();
         return clctx.statsAsync;
+    }
+
+    // Tracer::runBenchmark's timed loop (src/tracer.cpp:405-417 resetRenderer, :459-519): render for `seconds`,
+    // log the statistics every half second as the reference's CSV rows
+    //     scene;time;primary;extension;shadow;total;samples        (M rays or samples per second of that interval)
+    // and return the whole-run line `<scene>: %.1fM primary, ...` (:537-540).  The reference polls the clock after
+    // every iteration because each one ends in clFinish; here `batch` iterations are replayed from the CUDA graph
+    // between two polls (one host round trip per batch, not per iteration).
+    std::string runBenchmark(const std::string &sceneName, double seconds, std::ostream &csv, uint32_t batch = 8)
+    {
+        using clock = std::chrono::steady_clock;
+        auto now = [] { return std::chrono::duration<double>(clock::now().time_since_epoch()).count(); };
+        clctx.updateParams(params);
+        clctx.setPixelIndex(0);
+        clctx.render(0, true); // reset + priming segment
+        clctx.setPixelIndex(cursorStart());
+        clctx.finishQueue();
+        CudaContext::Totals prev = clctx.getRenderTotals(), first = prev, t = prev;
+        const double startT = now();
+        double lastLogTime = startT, currT = startT;
+        auto logStats = [&](double elapsed, double deltaT)
+        {
+            const double s = 1e6 * deltaT;
+            const double pr = double(t.primary - prev.primary), ex = double(t.extension - prev.extension), sh = double(t.shadow - prev.shadow);
+            csv << sceneName << ";" << elapsed << ";" << pr / s << ";" << ex / s << ";" << sh / s << ";" << (pr + ex + sh) / s << ";"
+                << double(t.samples - prev.samples) / s << "\n";
+            prev = t; lastLogTime = currT;
+        };
+        while (currT - startT < seconds)
+        {
+            clctx.render(batch);
+            t = clctx.getRenderTotals(); // synchronises
+            iteration += batch;
+            currT = now();
+            if (currT - lastLogTime > 0.5) logStats(currT - startT, currT - lastLogTime);
+        }
+        if (currT > lastLogTime) logStats(currT - startT, currT - lastLogTime);
+        clctx.enqueuePostprocessKernel(params);
+        clctx.finishQueue();
+        const double scale = 1e6 * (currT - startT);
+        const double prim = double(t.primary - first.primary) / scale, ext = double(t.extension - first.extension) / scale,
+                     shdw = double(t.shadow - first.shadow) / scale, samp = double(t.samples - first.samples) / scale;
+        char line[512];
+        snprintf(line, sizeof(line), "%s: %.1fM primary, %.2fM extension, %.2fM shadow, %.2fM samples, total: %.2fM rays/s",
+                 sceneName.c_str(), prim, ext, shdw, samp, prim + ext + shdw);
+        return line;
+    }
+
+    // Tracer::saveState / loadState (src/tracer.cpp:996-1054, keys F2/F3): camera, lights, sampling switches and
+    // post-processing as one flat little-endian record, field order as in iterateStateItems, so a
+    // data/states/state_<hash>.dat written by the reference's viewer positions this renderer's camera and vice versa.
+    // cameraRotation / cameraSpeed belong to the viewer's mouse handling: kept and written back unchanged.
+    void saveState(const std::string &file) { stateIO(file, true); }
+    void loadState(const std::string &file) { stateIO(file, false); clctx.updateParams(params); iteration = 0; }
+
+    // Accumulation checkpoint (new): the raw float4 buffer carries its own sample count in .w, so a
+    // progressive render resumes by loading it back before the next iterations.  Header: "FLXA", width, height.
+    void saveAccumulation(const std::string &file)
+    {
+        const std::vector<float> px = clctx.readPixels(FLX_BUF_PIXELS);
+        std::ofstream o(file, std::ios::binary);
+        if (!o) throw std::runtime_error("cannot write " + file);
+        const uint32_t hdr[3] = {0x41584c46u, params.width, params.height};
+        o.write((const char *)hdr, sizeof(hdr));
+        o.write((const char *)px.data(), (std::streamsize)(px.size() * sizeof(float)));
+    }
+    // call after the first render()/update() has reset the renderer (a reset clears the buffer)
+    void loadAccumulation(const std::string &file)
+    {
+        std::ifstream in(file, std::ios::binary);
+        uint32_t hdr[3] = {0, 0, 0};
+        if (!in || !in.read((char *)hdr, sizeof(hdr)) || hdr[0] != 0x41584c46u) throw std::runtime_error("not an accumulation checkpoint: " + file);
+        if (hdr[1] != params.width || hdr[2] != params.height) throw std::runtime_error("accumulation checkpoint has another resolution: " + file);
+        std::vector<float> px((size_t)params.width * params.height * 4);
+        if (!in.read((char *)px.data(), (std::streamsize)(px.size() * sizeof(float)))) throw std::runtime_error("truncated accumulation checkpoint: " + file);
+        clctx.writePixels(FLX_BUF_PIXELS, px);
     }
 
     // CLContext::saveImage (src/clcontext.cpp:404-483).  ".ppm": tonemapped preview, clamp, (uchar)(255*x), flipped
@@ -278,7 +361,26 @@ public:
         fclose(f);
     }
 
+    float cameraRotationX = 0.0f, cameraRotationY = 0.0f, cameraSpeed = 1.0f; // viewer state carried through state files
+
 private:
+    void stateIO(const std::string &file, bool write)
+    {
+        std::fstream io(file, std::ios::binary | (write ? std::ios::out : std::ios::in));
+        if (!io.good()) throw std::runtime_error("could not open state file " + file);
+        auto rw = [&](void *p, size_t n) { if (write) io.write((const char *)p, (std::streamsize)n); else io.read((char *)p, (std::streamsize)n); };
+        auto f = [&](float &v) { rw(&v, 4); };
+        auto u = [&](uint32_t &v) { rw(&v, 4); };
+        auto vec = [&](flx_float3 &v) { rw(&v.x, 4); rw(&v.y, 4); rw(&v.z, 4); };
+        flx_camera &c = params.camera; flx_area_light &l = params.areaLight;
+        f(cameraRotationX); f(cameraRotationY); f(cameraSpeed); f(c.fov);
+        if (!write) c.fovSCALE = std::tan(0.5f * c.fov * 0.01745329251994329576923690768489f);
+        f(c.focalDist); f(c.apertureSize); vec(c.dir); vec(c.pos); vec(c.right); vec(c.up);
+        vec(l.N); vec(l.pos); vec(l.right); vec(l.up); vec(l.E); f(l.size.x); f(l.size.y); f(params.envMapStrength);
+        u(params.maxBounces); u(params.useAreaLight); u(params.useEnvMap); u(params.sampleExpl); u(params.sampleImpl); u(params.useRoulette);
+        f(params.ppParams.exposure); u(params.ppParams.tmOperator);
+        if (!io.good()) throw std::runtime_error("state file " + file + (write ? ": write failed" : ": truncated"));
+    }
     CudaContext clctx; // name kept from the reference (src/tracer.hpp:131)
     int rank, worldSize;
 };

@@ -70,6 +70,21 @@ def allreduce_pixels(pixels, group=None):
     return pixels
 
 
+def reduce_frames(contexts):
+    """Several CudaContexts in THIS process, one per GPU (the layout the C++ host uses for `--gpus N`): sum their
+    accumulation buffers with the peer-memory kernel of csrc/flx_multi.cu (flx_reduce_frames) — the total ends up
+    in contexts[0], the others are zeroed.  No NCCL involved; for one process per GPU use allreduce_pixels."""
+    import ctypes as C
+    from ._lib import FluctusError
+    root = contexts[0]
+    handles = (C.c_void_p * len(contexts))(*[c.h for c in contexts])
+    rc = root.L.flx_reduce_frames(handles, len(contexts))
+    if rc != 0:
+        msgs = [c.L.flx_last_error(c.h).decode() for c in contexts] + [root.L.flx_last_error(None).decode()]
+        raise FluctusError("; ".join(m for m in msgs if m) or "flx_reduce_frames failed (%d)" % rc)
+    return root
+
+
 def normalise(pixels):
     """rgb / sample count — what CLContext::saveImage does for .hdr output (clcontext.cpp:455-470)."""
     px = np.asarray(pixels, np.float32).reshape(-1, 4)

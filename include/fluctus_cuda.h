@@ -132,6 +132,16 @@ int flx_read_pixels(flx_ctx *ctx, int which /* flx_buffer */, void *host_out, si
 void *flx_device_ptr(flx_ctx *ctx, int which /* flx_buffer */); /* for the per-frame all-reduce */
 int flx_pick(flx_ctx *ctx, float ndc_x, float ndc_y, flx_hit *out);
 
+/* ---- multi-GPU frame combine inside one process (new; SURVEY.md §8e — the reference is single-device) ---------
+ * ctxs[0..n): contexts on different GPUs rendering sample shards of the same frame (same resolution, seeds offset
+ * with flx_set_options).  Drains their streams, then sums the accumulation buffers (and the denoiser AOV sums when
+ * enabled) element-wise in rank order: afterwards ctxs[0] holds the total — run flx_postprocess / flx_read_pixels
+ * on it — and the other buffers are zero, so all contexts may go on accumulating and be combined again.  The sum is
+ * a kernel over NVLink peer memory (GPU d combines rows slice d from all N buffers); without peer access the frames
+ * are staged through the root.  With one process per GPU use an NCCL all-reduce of flx_device_ptr(ctx,
+ * FLX_BUF_PIXELS) instead (fluctus_b200/multi_gpu.py).  Synchronises. */
+int flx_reduce_frames(flx_ctx *const *ctxs, int n);
+
 /* ---- parallel hierarchy build (new) --------------------------------------------------------
  * Linear BVH (63-bit Morton order + Karras' radix tree, subtrees of <= max_leaf triangles collapsed into one leaf)
  * built on GPU `device` and returned in the reference's own format — Node[] in depth-first order with the left

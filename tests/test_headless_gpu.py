@@ -110,3 +110,147 @@ def test_headless_gpu_built_hierarchy_renders_the_same_image(tmp_path, teapot, n
         imgs.append(_read_pfm(out))
     same = (imgs[0].view(np.uint32) == imgs[1].view(np.uint32)).all(-1)
     assert same.mean() >= 0.995, same.mean()
+
+
+def _run(args):
+    r = subprocess.run([BIN] + [str(a) for a in args], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return r
+
+
+def _teapot_job(tmp_path, teapot, night_env, N=8192, bounces=4):
+    from fluctus_b200 import scene as fs
+    flxs, cfg = str(tmp_path / "teapot.flxs"), str(tmp_path / "settings.json")
+    fs.save_flxs(flxs, teapot, night_env)
+    json.dump({"release": {"wfBufferSize": N, "useAreaLight": False, "maxPathDepth": bounces, "tonemap": 2}}, open(cfg, "w"))
+    return flxs, cfg
+
+
+def test_headless_benchmark_mode_writes_the_reference_csv(tmp_path, teapot, night_env):
+    """Tracer::runBenchmark (src/tracer.cpp:391-565): CSV `scene;time;primary;extension;shadow;total;samples`, one row
+    per half second of rendering (M rays / samples per second of the interval), total = primary + extension + shadow,
+    and the reference's one-line summary per scene."""
+    flxs, cfg = _teapot_job(tmp_path, teapot, night_env, N=65536)
+    csv = str(tmp_path / "bench.csv")
+    r = _run(["-x", 256, "-y", 256, "--settings", cfg, "--benchmark", 1.6, "--csv", csv, "--out", tmp_path / "b.ppm", flxs])
+    lines = open(csv).read().strip().splitlines()
+    assert lines[0] == "scene;time;primary;extension;shadow;total;samples"
+    rows = [l.split(";") for l in lines[1:]]
+    assert 3 <= len(rows) <= 5, lines
+    t_prev = 0.0
+    for row in rows:
+        assert row[0] == flxs and len(row) == 7
+        t, prim, ext, shw, tot, smp = (float(x) for x in row[1:])
+        assert t > t_prev and prim > 0 and ext > 0 and smp > 0
+        assert abs(tot - (prim + ext + shw)) <= 1e-3 * tot
+        assert abs(prim - smp) <= 0.05 * prim  # a regenerated path is a primary ray and a finished sample
+        t_prev = t
+    assert 1.6 <= t_prev < 2.6
+    summary = [l for l in r.stdout.splitlines() if "M primary" in l]
+    assert len(summary) == 1 and summary[0].startswith(flxs + ": ") and "total:" in summary[0]
+    stats = json.loads(r.stdout.strip().splitlines()[-1])
+    assert stats["samples"] > 0 and os.path.getsize(tmp_path / "b.ppm") > 256 * 256 * 3
+
+
+def test_headless_state_file_roundtrip_moves_the_camera(tmp_path, teapot, night_env):
+    """data/states/state_<hash>.dat (Tracer::iterateStateItems, src/tracer.cpp:996-1054): 46 little-endian words in the
+    reference's field order.  A saved state loads back to the same image statistics; a state with another camera
+    position renders another image."""
+    flxs, cfg = _teapot_job(tmp_path, teapot, night_env)
+    st, st2 = str(tmp_path / "state.dat"), str(tmp_path / "state2.dat")
+    a_img, b_img, c_img = (str(tmp_path / n) for n in ("a.pfm", "b.pfm", "c.pfm"))
+    common = ["-x", 96, "-y", 64, "-s", 16, "--settings", cfg]
+    _run(common + ["--save-state", st, "--out", a_img, flxs])
+    raw = np.fromfile(st, np.uint8)
+    assert raw.size == 46 * 4
+    f, u = raw.view(np.float32), raw.view(np.uint32)
+    assert f[3] == 60.0 and tuple(f[9:12]) == (0.0, 1.0, 3.5) and tuple(f[6:9]) == (0.0, 0.0, -1.0)   # fov, pos, dir
+    assert tuple(f[30:33]) == (100.0, 100.0, 100.0) and f[33] == 0.5 and f[35] == 1.0                    # light E, size, env strength
+    assert u[36] == 4 and u[37] == 0 and u[38] == 1 and u[39] == 1 and u[40] == 1 and u[41] == 0 and u[43] == 2
+    _run(common + ["--load-state", st, "--out", b_img, flxs])
+    a, b = _read_pfm(a_img), _read_pfm(b_img)
+    assert abs(a.mean() - b.mean()) < 0.03 * a.mean()
+    moved = f.copy(); moved[9:12] = (1.5, 1.2, 3.0)
+    moved.tofile(st2)
+    _run(common + ["--load-state", st2, "--out", c_img, flxs])
+    c = _read_pfm(c_img)
+    assert float(((_binned(a) - _binned(c)) ** 2).mean()) > 20 * float(((_binned(a) - _binned(b)) ** 2).mean())
+    r = subprocess.run([BIN, "--load-state", str(tmp_path / "missing.dat"), flxs], capture_output=True, text=True)
+    assert r.returncode != 0 and "state file" in r.stderr
+
+
+def test_headless_accumulation_checkpoint_resumes(tmp_path, teapot, night_env):
+    """--save-accum / --load-accum: the raw float4 buffer carries its sample count in .w, so 8 spp + 8 more spp on top of
+    the checkpoint hold as many samples as a 16 spp render and show the same image."""
+    flxs, cfg = _teapot_job(tmp_path, teapot, night_env)
+    acc, acc2 = str(tmp_path / "a.flxa"), str(tmp_path / "b.flxa")
+    common = ["-x", 96, "-y", 64, "--settings", cfg]
+    _run(common + ["-s", 8, "--save-accum", acc, "--out", tmp_path / "p1.pfm", flxs])
+    _run(common + ["-s", 8, "--load-accum", acc, "--save-accum", acc2, "--out", tmp_path / "p2.pfm", flxs])
+    _run(common + ["-s", 16, "--out", tmp_path / "full.pfm", flxs])
+
+    def load(p):
+        raw = np.fromfile(p, np.uint8)
+        hdr = raw[:12].view(np.uint32)
+        assert hdr[0] == 0x41584c46 and hdr[1] == 96 and hdr[2] == 64
+        return raw[12:].view(np.float32).reshape(64, 96, 4)
+    n1, n2 = load(acc)[..., 3].sum(), load(acc2)[..., 3].sum()
+    assert n1 >= 8 * 96 * 64 and n2 >= n1 + 8 * 96 * 64
+    p2, full = _read_pfm(str(tmp_path / "p2.pfm")), _read_pfm(str(tmp_path / "full.pfm"))
+    x, y = _binned(p2), _binned(full)
+    assert float((((x - y) ** 2) / (y ** 2 + 1e-3)).mean()) < 0.05
+    r = subprocess.run([BIN, "-x", 64, "-y", 64, "--settings", cfg, "--load-accum", acc, flxs], capture_output=True, text=True)
+    assert r.returncode != 0 and "resolution" in r.stderr
+
+
+def _gpu_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+def test_reduce_frames_over_peer_memory(teapot, night_env):
+    """flx_reduce_frames: contexts on two GPUs in one process; the total lands in context 0 bit-exactly as
+    (frame0 + frame1) in rank order, context 1 is zeroed, and a second combine is a no-op."""
+    if _gpu_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    from fluctus_b200 import Tracer
+    from fluctus_b200.multi_gpu import reduce_frames
+    W, H, N = 160, 96, 16384
+    trs = []
+    for r in range(2):
+        tr = Tracer(W, H, num_tasks=N, max_bounces=4, use_env_map=True, use_area_light=False, device=r, rank=r, world_size=2)
+        tr.init(teapot, night_env)
+        tr.render(spp=8, batch=8)
+        trs.append(tr)
+    f0, f1 = trs[0].pixels().copy(), trs[1].pixels().copy()
+    assert not np.array_equal(f0, f1) and f1[..., 3].sum() >= 8 * W * H
+    reduce_frames([t.clctx for t in trs])
+    total = trs[0].pixels()
+    assert np.array_equal(total.view(np.uint32), (f0 + f1).view(np.uint32))
+    assert not trs[1].pixels().any()
+    reduce_frames([t.clctx for t in trs])
+    assert np.array_equal(trs[0].pixels().view(np.uint32), total.view(np.uint32))
+    for t in trs:
+        t.close()
+
+
+def test_headless_two_gpus_render_one_frame(tmp_path, teapot, night_env):
+    """fluctus_headless --gpus 2: both shards' samples are in the image (sample counts add up), and the image matches
+    the single-GPU render of the same budget."""
+    if _gpu_count() < 2:
+        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    flxs, cfg = _teapot_job(tmp_path, teapot, night_env)
+    common = ["-x", 96, "-y", 64, "-s", 32, "--settings", cfg]
+    r2 = _run(common + ["--gpus", 2, "--save-accum", tmp_path / "two.flxa", "--out", tmp_path / "two.pfm", flxs])
+    r1 = _run(common + ["--out", tmp_path / "one.pfm", flxs])
+    s2, s1 = json.loads(r2.stdout.strip().splitlines()[-1]), json.loads(r1.stdout.strip().splitlines()[-1])
+    assert s2["gpus"] == 2 and s2["samples"] >= 32 * 96 * 64 and s2["samples"] >= 0.9 * s1["samples"]
+    acc = np.fromfile(tmp_path / "two.flxa", np.uint8)[12:].view(np.float32).reshape(64, 96, 4)
+    assert abs(acc[..., 3].sum() - s2["samples"]) <= 0.02 * s2["samples"]  # samples still in flight at the end are not splatted
+    x, y = _binned(_read_pfm(str(tmp_path / "two.pfm"))), _binned(_read_pfm(str(tmp_path / "one.pfm")))
+    assert float((((x - y) ** 2) / (y ** 2 + 1e-3)).mean()) < 0.05
+    rm = _run(["-x", 96, "-y", 64, "-s", 5, "--settings", cfg, "--renderer", "mk", "--gpus", 2, "--save-accum", tmp_path / "mk.flxa",
+               "--out", tmp_path / "mk.pfm", flxs])
+    mk = np.fromfile(tmp_path / "mk.flxa", np.uint8)[12:].view(np.float32).reshape(64, 96, 4)
+    assert np.all(mk[..., 3] == 5.0)  # exact spp: 3 samples from rank 0 + 2 from rank 1 in every pixel
+    assert json.loads(rm.stdout.strip().splitlines()[-1])["gpus"] == 2

@@ -164,6 +164,33 @@ def test_deep_chain_hierarchy(ctx, oracle, teapot):
     ctx.uploadSceneData(teapot)
 
 
+def test_host_batch_pipeline_chunk_boundaries(ctx, oracle, teapot):
+    """flx_trace_closest / flx_trace_any with host buffers run as an upload / traverse / download pipeline over chunks of
+    2^20 rays: a batch that ends 777 rays into its third chunk (and pageable, not pinned, memory) must give what one
+    device-resident launch gives, and the rays either side of every chunk boundary must match the oracle."""
+    import torch
+    from fluctus_b200 import scene as fs
+    ctx.uploadSceneData(teapot)
+    n = (2 << 20) + 777
+    rays = fs.bench_rays(n, teapot["bounds"])
+    hit_i, hit_t, hits = ctx.traceClosest(rays, want_hits=True)
+    d_rays = torch.from_numpy(rays).cuda()
+    d_i = torch.empty(n, dtype=torch.int32, device="cuda"); d_t = torch.empty(n, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    ctx.traceClosestDevice(d_rays.data_ptr(), n, d_i.data_ptr(), d_t.data_ptr())
+    ctx.finishQueue()
+    assert np.array_equal(hit_i, d_i.cpu().numpy()) and np.array_equal(bits(hit_t), bits(d_t.cpu().numpy()))
+    h = hit_i >= 0
+    assert np.array_equal(hits["i"][h], hit_i[h]) and np.array_equal(bits(hits["t"][h]), bits(hit_t[h]))
+    sel = np.concatenate([np.arange(0, 512), np.arange((1 << 20) - 512, (1 << 20) + 512),
+                          np.arange((2 << 20) - 512, (2 << 20) + 512), np.arange(n - 1024, n)])
+    ref = oracle.trace_closest(teapot, rays[sel], 0)
+    assert np.array_equal(hit_i[sel], ref["hit_i"]) and np.array_equal(bits(hit_t[sel]), bits(ref["hit_t"]))
+    occ = ctx.traceAny(rays)
+    assert np.array_equal(occ != 0, hit_i >= 0)  # tmax = FLT_MAX: occluded <=> some hit
+    assert np.array_equal(occ[sel], oracle.trace_any(teapot, rays[sel], 0))
+
+
 def test_cfg5_full_size_microbench_parity(oracle, teapot):
     """BASELINE config 5 at full size: 15x15x14 replicated teapots (10 098 900 triangles), 2^24 incoherent rays.
     Oracle comparison (bit-exact index + distance) on the first 2^19 rays; size-independent properties on all of
