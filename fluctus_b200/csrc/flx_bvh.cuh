@@ -47,6 +47,19 @@ FLX_DEV void stageTopNodes(const DevBVH &bvh, float4 *top)
 
 #define FLX_STACK_SIZE 64 // reference: uint stack[64] (src/bvh.cl:240)
 
+// One 256-bit load (sm_100: LDG.E.256) = half an inner node.  Rays of a warp sit in different nodes, so every lane of
+// a load instruction costs the L1 its own tag look-up whatever the access width: fetching the 64-byte node with two
+// 32-byte loads instead of four 16-byte ones halves the L1 wavefronts of a node visit.
+#ifndef FLX_NODE_LD256
+#define FLX_NODE_LD256 0
+#endif
+FLX_DEV void ldg256(const float4 *p, float4 &a, float4 &b)
+{
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+        : "l"(p));
+}
+
 // src/intersect.cl:41-60 with dinv hoisted (same value each time => same bits)
 FLX_DEV bool slabTest(float bx0, float by0, float bz0, float bx1, float by1, float bz1,
                       f3 o, f3 dinv, float tMaxPrev, float &tnear)
@@ -248,7 +261,11 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                     else
                     {
                         const float4 *n = bvh.nodes + 4 * (size_t)cur;
+#if FLX_NODE_LD256
+                        ldg256(n, n0, n1); ldg256(n + 2, n2, n3);
+#else
                         n0 = __ldg(n); n1 = __ldg(n + 1); n2 = __ldg(n + 2); n3 = __ldg(n + 3);
+#endif
                     }
                     float lnear, rnear;
                     const bool lh = slabTest(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, o, dinv, best.t, lnear);

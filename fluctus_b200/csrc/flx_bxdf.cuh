@@ -9,14 +9,19 @@
 
 struct Mat // register copy of flx_material (glossy.cl:28 edits its private copy too)
 {
-    f3 Kd, Ks, Ke;
+    f3 Kd, Ks, Ke; // Kd: already raised to 2.2 (the only consumer is matGetAlbedo; see MaterialsDev::gammaLut)
     float Ns, Ni;
     int map_Kd, map_Ks, type;
 };
 FLX_DEV Mat loadMat(const flx_material *__restrict__ m)
 {
     const float4 *p = (const float4 *)m;
-    const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), e = __ldg(p + 4), f = __ldg(p + 5);
+#ifdef FLX_GAMMA_PER_PATH
+    const float4 a = __ldg(p);
+#else
+    const float4 a = __ldg(p + 3); // Kt slot of the device copy = powf(Kd, 2.2f) (k_prepare_materials)
+#endif
+    const float4 b = __ldg(p + 1), c = __ldg(p + 2), e = __ldg(p + 4), f = __ldg(p + 5);
     Mat r;
     r.Kd = mk3(a); r.Ks = mk3(b); r.Ke = mk3(c);
     r.Ns = e.x; r.Ni = e.y; r.map_Kd = __float_as_int(e.w);

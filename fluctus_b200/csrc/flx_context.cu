@@ -2,6 +2,7 @@
 // dispatch, read-back.  Replaces the reference's CLContext (src/clcontext.cpp); there is no CPU
 // or library fallback — without an sm_100 device flx_create fails.
 #include "flx_internal.h"
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 
@@ -116,7 +117,7 @@ void flx_destroy(flx_ctx *ctx)
     drainTimers(ctx);
     invalidateGraph(ctx);
     cudaFree(ctx->dNodes); cudaFree(ctx->dSlots); cudaFree(ctx->dShade);
-    cudaFree(ctx->dMaterials); cudaFree(ctx->dTextures); cudaFree(ctx->dTexels); cudaFree(ctx->dTris160);
+    cudaFree(ctx->dMaterials); cudaFree(ctx->dTextures); cudaFree(ctx->dTexels); cudaFree(ctx->dTris160); cudaFree(ctx->dGammaLut);
     cudaFree(ctx->dEnv); cudaFree(ctx->dProb); cudaFree(ctx->dPdf); cudaFree(ctx->dAlias);
     cudaFree(ctx->stateBlock); cudaFree(ctx->queueBlock); cudaFree(ctx->fbBlock); cudaFree(ctx->dScratch);
     if (ctx->hCounters) cudaFreeHost(ctx->hCounters);
@@ -125,6 +126,20 @@ void flx_destroy(flx_ctx *ctx)
     if (ctx->copyOut) cudaStreamDestroy(ctx->copyOut);
     if (ctx->ownStream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+// see MaterialsDev::gammaLut
+__global__ void k_prepare_materials(flx_material *materials, int nMaterials, float *gammaLut)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 256) gammaLut[i] = powf((float)i * FLX_ONE_255, 2.2f);
+    if (i < nMaterials)
+    {
+        const flx_float3 kd = materials[i].Kd;
+        flx_float3 g = kd;
+        g.x = powf(kd.x, 2.2f); g.y = powf(kd.y, 2.2f); g.z = powf(kd.z, 2.2f);
+        materials[i].Kt = g;
+    }
 }
 
 int flx_upload_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, const uint32_t *indices, size_t n_indices,
@@ -172,6 +187,14 @@ int flx_upload_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, cons
         FLX_CUDA(ctx, cudaMalloc(&ctx->dTris160, n_tris * sizeof(flx_triangle)));
         FLX_CUDA(ctx, cudaMemcpy(ctx->dTris160, tris, n_tris * sizeof(flx_triangle), cudaMemcpyHostToDevice));
     }
+    if (!ctx->dGammaLut) FLX_CUDA(ctx, cudaMalloc(&ctx->dGammaLut, 256 * sizeof(float)));
+    {
+        const int n = (int)std::max<size_t>(n_materials, 256);
+        k_prepare_materials<<<(n + 255) / 256, 256, 0, ctx->stream>>>(ctx->dMaterials, (int)n_materials, ctx->dGammaLut);
+        FLX_CUDA(ctx, cudaGetLastError());
+        FLX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->mats.gammaLut = ctx->dGammaLut;
     ctx->mats.materials = ctx->dMaterials; ctx->mats.nMaterials = (int)n_materials;
     ctx->mats.textures = ctx->dTextures; ctx->mats.nTextures = (int)n_textures;
     ctx->mats.texels = ctx->dTexels; ctx->mats.tris160 = ctx->dTris160;

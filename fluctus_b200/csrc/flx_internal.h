@@ -59,6 +59,11 @@ struct MaterialsDev
     const flx_tex_desc *textures; int nTextures;
     const uint8_t *texels;
     const flx_triangle *tris160; // original triangles: only read for normal-mapped hits (utils.cl:184-190)
+    // albedo gamma (utils.cl:161-166) taken out of the per-path work: gammaLut[k] = powf((float)k * (1/255), 2.2f) for
+    // the 256 values an RGBA8 texel can take, and the DEVICE copy of every material carries powf(Kd, 2.2f) in its Kt
+    // slot (Kt is not read by any kernel).  Both are computed on the device with the powf the shading kernels would
+    // have called on the same input bits, so shaded values are bit-identical to evaluating it per path.
+    const float *gammaLut;
 };
 
 struct FrameBuffers
@@ -113,6 +118,7 @@ struct flx_ctx
     size_t nInner = 0, nSlots = 0, nTris = 0;
     MaterialsDev mats{}; flx_material *dMaterials = nullptr; flx_tex_desc *dTextures = nullptr; uint8_t *dTexels = nullptr;
     flx_triangle *dTris160 = nullptr;
+    float *dGammaLut = nullptr;
     bool sceneReady = false;
     bool traceSetupDone = false; // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) done on this device
     EnvMapDev env{}; float4 *dEnv = nullptr; float *dProb = nullptr, *dPdf = nullptr; int *dAlias = nullptr;

@@ -170,7 +170,7 @@ k_mk_bsdf(PathState st, FrameBuffers fb, MaterialsDev md, EnvMapDev env, flx_ren
                 if (!FLX_BXDF_IS_SINGULAR(mat.type) && !(flags & 2u))
                 {
                     st.logicFlags[gid] = flags | 2u;
-                    const f3 albedo = matGetFloat3(mat.Kd, hit.uvx, hit.uvy, mat.map_Kd, md);
+                    const f3 albedo = matGetFloat3(mk3(__ldg((const float4 *)mp)), hit.uvx, hit.uvy, mat.map_Kd, md); // raw Kd: no gamma on the AOV
                     float4 a = fb.denoiserAlbedo[gid];
                     a.x += albedo.x; a.y += albedo.y; a.z += albedo.z; a.w += 1.0f;
                     fb.denoiserAlbedo[gid] = a;

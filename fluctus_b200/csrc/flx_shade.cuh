@@ -68,7 +68,7 @@ FLX_DEV f3 cosSampleHemisphere(f3 n, uint32_t &seed, float &pdf)
 }
 
 // utils.cl:139-158: nearest texel, repeat wrap (unsigned modulo as OpenCL evaluates int % uint)
-FLX_DEV f3 readTexture(float uvx, float uvy, const flx_tex_desc &tex, const uint8_t *__restrict__ data)
+FLX_DEV uchar4 readTexel(float uvx, float uvy, const flx_tex_desc &tex, const uint8_t *__restrict__ data)
 {
     const uint32_t width = tex.width, height = tex.height;
     uvx *= (float)width;
@@ -80,7 +80,11 @@ FLX_DEV f3 readTexture(float uvx, float uvy, const flx_tex_desc &tex, const uint
     int cy = (int)((float)ty + uvy - fy);
     cx = min(max(cx, 0), (int)width - 1);
     cy = min(max(cy, 0), (int)height - 1);
-    const uchar4 p = *(const uchar4 *)(data + tex.offset + (uint32_t)cx * 4u + (uint32_t)cy * width * 4u);
+    return *(const uchar4 *)(data + tex.offset + (uint32_t)cx * 4u + (uint32_t)cy * width * 4u);
+}
+FLX_DEV f3 readTexture(float uvx, float uvy, const flx_tex_desc &tex, const uint8_t *__restrict__ data)
+{
+    const uchar4 p = readTexel(uvx, uvy, tex, data);
     f3 c = mk3((float)p.x, (float)p.y, (float)p.z);
     c *= FLX_ONE_255;
     return c;
@@ -91,9 +95,17 @@ FLX_DEV f3 matGetFloat3(f3 fallback, float uvx, float uvy, int idx, const Materi
 {
     return (idx != -1) ? readTexture(uvx, uvy, m.textures[idx], m.texels) : fallback;
 }
-FLX_DEV f3 matGetAlbedo(f3 fallback, float uvx, float uvy, int idx, const MaterialsDev &m)
+// pow(matGetFloat3(...), 2.2f) of utils.cl:161-166 without a powf per path: `fallbackGamma` is the material's
+// pre-raised constant, texels go through the 256-entry table (MaterialsDev::gammaLut) — same bits either way.
+FLX_DEV f3 matGetAlbedo(f3 fallbackGamma, float uvx, float uvy, int idx, const MaterialsDev &m)
 {
-    return pow3(matGetFloat3(fallback, uvx, uvy, idx, m), 2.2f);
+#ifdef FLX_GAMMA_PER_PATH
+    return pow3(matGetFloat3(fallbackGamma, uvx, uvy, idx, m), 2.2f); // fallbackGamma = raw Kd in this build (loadMat)
+#else
+    if (idx == -1) return fallbackGamma;
+    const uchar4 p = readTexel(uvx, uvy, m.textures[idx], m.texels);
+    return mk3(__ldg(m.gammaLut + p.x), __ldg(m.gammaLut + p.y), __ldg(m.gammaLut + p.z));
+#endif
 }
 
 // utils.cl:251-259

@@ -153,7 +153,7 @@ def test_headless_benchmark_mode_writes_the_reference_csv(tmp_path, teapot, nigh
 
 
 def test_headless_state_file_roundtrip_moves_the_camera(tmp_path, teapot, night_env):
-    """data/states/state_<hash>.dat (Tracer::iterateStateItems, src/tracer.cpp:996-1054): 46 little-endian words in the
+    """data/states/state_<hash>.dat (Tracer::iterateStateItems, src/tracer.cpp:996-1054): 44 little-endian words in the
     reference's field order.  A saved state loads back to the same image statistics; a state with another camera
     position renders another image."""
     flxs, cfg = _teapot_job(tmp_path, teapot, night_env)
@@ -162,7 +162,7 @@ def test_headless_state_file_roundtrip_moves_the_camera(tmp_path, teapot, night_
     common = ["-x", 96, "-y", 64, "-s", 16, "--settings", cfg]
     _run(common + ["--save-state", st, "--out", a_img, flxs])
     raw = np.fromfile(st, np.uint8)
-    assert raw.size == 46 * 4
+    assert raw.size == 44 * 4
     f, u = raw.view(np.float32), raw.view(np.uint32)
     assert f[3] == 60.0 and tuple(f[9:12]) == (0.0, 1.0, 3.5) and tuple(f[6:9]) == (0.0, 0.0, -1.0)   # fov, pos, dir
     assert tuple(f[30:33]) == (100.0, 100.0, 100.0) and f[33] == 0.5 and f[35] == 1.0                    # light E, size, env strength
@@ -199,7 +199,7 @@ def test_headless_accumulation_checkpoint_resumes(tmp_path, teapot, night_env):
     p2, full = _read_pfm(str(tmp_path / "p2.pfm")), _read_pfm(str(tmp_path / "full.pfm"))
     x, y = _binned(p2), _binned(full)
     assert float((((x - y) ** 2) / (y ** 2 + 1e-3)).mean()) < 0.05
-    r = subprocess.run([BIN, "-x", 64, "-y", 64, "--settings", cfg, "--load-accum", acc, flxs], capture_output=True, text=True)
+    r = subprocess.run([BIN, "-x", "64", "-y", "64", "--settings", cfg, "--load-accum", acc, flxs], capture_output=True, text=True)
     assert r.returncode != 0 and "resolution" in r.stderr
 
 

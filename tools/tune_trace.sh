@@ -2,7 +2,7 @@
 # Rebuild the traversal TUs with extra -D flags and print render value, stage times and the cfg5 ray-cast figures
 # for each set (run on the GPU box).  usage: tools/tune_trace.sh "" "-DFLX_PF_PUSH=1" "-DFLX_PF_PUSH=1 -DFLX_PF_CUR=1" ...
 cd "$(dirname "$0")/.."
-TUS="fluctus_b200/csrc/flx_trace.cu fluctus_b200/csrc/flx_microkernel.cu fluctus_b200/csrc/flx_repack.cu fluctus_b200/csrc/flx_api.cu"
+TUS="$(ls fluctus_b200/csrc/*.cu)"
 for defs in "$@"; do
   touch $TUS
   make -s -j4 -C fluctus_b200/csrc EXTRA="$defs" || exit 1
