@@ -314,6 +314,13 @@ def run_raycast(dev, rank, world, teapot, peak_gbs, steps, warmup, check):
                        "hit_fraction": cnt["hits"] / max(cnt["rays"], 1), "algorithmic_bytes": per_ray},
            "roofline": {"bound": "hbm", "kernel": "k_trace_batch", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                         "frac": achieved / peak_gbs, "traffic": None, "kernel_ms": out["kernel_ms"]}}
+    try:  # DRAM bytes per launch from the committed ncu --set full capture of this kernel (same batch, same scene)
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("raycast")
+        if t and int(t.get("rays", 0)) == n:
+            res["roofline"].update({"traffic": t["dram_bytes_per_launch"] / 1e9, "traffic_unit": "GB per launch (DRAM read + write)",
+                                    "traffic_source": t["source"]})
+    except (OSError, ValueError, KeyError):
+        pass
     if check and rank == 0:  # spot parity against the oracle (checker only; tests/ hold the full comparison)
         from oracle import pyoracle
         m = 1 << 15

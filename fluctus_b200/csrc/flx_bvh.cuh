@@ -143,6 +143,19 @@ struct TravCount { unsigned int inner, leaf, tri; };
 #ifndef FLX_STAY_INNER
 #define FLX_STAY_INNER 12
 #endif
+// any-hit rays (shorter traversals, early exit) may take their own thresholds; default: the same
+#ifndef FLX_VOTE_RETIRE_ANY
+#define FLX_VOTE_RETIRE_ANY FLX_VOTE_RETIRE
+#endif
+#ifndef FLX_VOTE_LEAF_ANY
+#define FLX_VOTE_LEAF_ANY FLX_VOTE_LEAF
+#endif
+#ifndef FLX_STAY_LEAF_ANY
+#define FLX_STAY_LEAF_ANY FLX_STAY_LEAF
+#endif
+#ifndef FLX_STAY_INNER_ANY
+#define FLX_STAY_INNER_ANY FLX_STAY_INNER
+#endif
 #define FLX_TRAV_DONE ((int)0x80000000) // not a valid ref: leaf refs are ~slot with slot < 0x7fffffff
 
 // Prefetch hints (experiment switches): FLX_PF_CUR covers the record a lane steps to next (it
@@ -170,6 +183,8 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
 {
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
+    constexpr int VOTE_RETIRE = ANY ? FLX_VOTE_RETIRE_ANY : FLX_VOTE_RETIRE, VOTE_LEAF = ANY ? FLX_VOTE_LEAF_ANY : FLX_VOTE_LEAF;
+    constexpr int STAY_LEAF = ANY ? FLX_STAY_LEAF_ANY : FLX_STAY_LEAF, STAY_INNER = ANY ? FLX_STAY_INNER_ANY : FLX_STAY_INNER;
     int stack[FLX_STACK_SIZE];
     int sp = 0, cur = FLX_TRAV_DONE;
     bool active = false, poolEmpty = false;
@@ -186,7 +201,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
         const unsigned runnable = mInner | mLeaf;
         const int waiting = __popc(mDone | mIdle);
 
-        if (waiting >= FLX_VOTE_RETIRE || (runnable == 0u && waiting > 0))
+        if (waiting >= VOTE_RETIRE || (runnable == 0u && waiting > 0))
         {
             // ---- retire finished rays, hand the next rays of the pool to the free lanes ----------------
             if (isDone) { job.store(best, o, d); active = false; }
@@ -215,7 +230,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
             }
         }
         else if (runnable == 0u) break; // nothing running, nothing to retire, pool empty
-        else if (mLeaf != 0u && (__popc(mLeaf) >= FLX_VOTE_LEAF || mInner == 0u))
+        else if (mLeaf != 0u && (__popc(mLeaf) >= VOTE_LEAF || mInner == 0u))
         {
             // ---- triangle tests, one per waiting lane and pass: leaf slots in index order, strictly-closer
             // wins.  The warp stays in this body while enough lanes still hold leaf work (one ballot per pass
@@ -242,7 +257,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                     prefetchRef<FLX_PF_CUR>(bvh, cur);
                 }
                 m = __ballot_sync(FULL, active && cur < 0 && cur != FLX_TRAV_DONE);
-            } while (__popc(m) >= FLX_STAY_LEAF);
+            } while (__popc(m) >= STAY_LEAF);
         }
         else
         {
@@ -286,7 +301,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                     prefetchRef<FLX_PF_CUR>(bvh, cur);
                 }
                 m = __ballot_sync(FULL, active && cur >= 0);
-            } while (__popc(m) >= FLX_STAY_INNER);
+            } while (__popc(m) >= STAY_INNER);
         }
     }
 }

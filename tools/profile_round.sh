@@ -12,4 +12,10 @@ CMD="python bench.py --steps 2 --warmup 3 --no-raycast --no-cpu-baseline"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launch.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_ext_shadow" --launch-skip 100 -c 1 -o gpurun_out/${TAG}_k_ext_shadow $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
 tail -2 gpurun_out/${TAG}_ncu_full.log
+#   4. the shading stages (logic + the fused material launch) at the same steady-state iteration,
+#   5. the cfg5 ray-cast kernel (10.1 M triangles, 2^24 incoherent rays): the HBM-facing case.
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_logic|k_materials" --launch-skip 200 -c 2 -o gpurun_out/${TAG}_shade $CMD > gpurun_out/${TAG}_ncu_shade.log 2>&1
+tail -1 gpurun_out/${TAG}_ncu_shade.log
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_trace_batch" --launch-skip 4 -c 1 -o gpurun_out/${TAG}_k_trace_batch python tools/raycast_only.py 2 > gpurun_out/${TAG}_ncu_raycast.log 2>&1
+tail -1 gpurun_out/${TAG}_ncu_raycast.log
 cut -c1-400 gpurun_out/${TAG}_bench.json
