@@ -40,7 +40,7 @@ int ensureScratch(flx_ctx *ctx, size_t bytes)
 int stageLogic(flx_ctx *ctx, int first) { TimerScope t(ctx, 2); return flx_launch_logic(ctx, first); }
 int stageLogicRegen(flx_ctx *ctx) { TimerScope t(ctx, 2); return flx_launch_logic_regen(ctx); }
 int stageRaygen(flx_ctx *ctx) { TimerScope t(ctx, 3); return flx_launch_raygen(ctx); }
-int stageMaterials(flx_ctx *ctx) { TimerScope t(ctx, 4); return flx_launch_materials(ctx); }
+int stageMaterials(flx_ctx *ctx, bool renderEntry = false) { TimerScope t(ctx, 4); return flx_launch_materials(ctx, renderEntry); }
 int stageExt(flx_ctx *ctx) { TimerScope t(ctx, 0); return flx_launch_ext(ctx); }
 int stageShadow(flx_ctx *ctx) { TimerScope t(ctx, 1); return flx_launch_shadow(ctx); }
 int stageExtShadow(flx_ctx *ctx) { TimerScope t(ctx, 0); return flx_launch_ext_shadow(ctx); } // timed under the extension stage
@@ -49,7 +49,7 @@ int stageExtShadow(flx_ctx *ctx) { TimerScope t(ctx, 0); return flx_launch_ext_s
 int enqueueIteration(flx_ctx *ctx)
 {
     FLX_TRY(stageLogicRegen(ctx)); // logic + raygen: terminated paths restart inside the logic kernel
-    FLX_TRY(stageMaterials(ctx));
+    FLX_TRY(stageMaterials(ctx, true));
     if (ctx->counting) // the visit counters are kept per stage
     {
         FLX_TRY(stageExt(ctx));

@@ -129,6 +129,7 @@ struct TravCount { unsigned int inner, leaf, tri; };
 // enough peers join them.  Thresholds were tuned on B200 with tools/tune_vote.sh (kitchen render + cfg5 rays); re-tuned
 // for the 2^22-path pool and the fused extension+shadow launch: 12/8/4/8 -> 16/6/3/12 is +7 % on the kitchen, cfg5 unchanged.
 // A Job supplies the rays and consumes the results:
+//     static constexpr bool BATCH                        // which threshold set the loop uses (see below)
 //     bool load(unsigned k, f3 &o, f3 &d, float &tmax)   // false: ray k needs no traversal (already resolved)
 //     void store(const RayHit &h, f3 o, f3 d)            // result of the ray loaded last by this lane
 #ifndef FLX_VOTE_RETIRE
@@ -142,6 +143,22 @@ struct TravCount { unsigned int inner, leaf, tri; };
 #endif
 #ifndef FLX_STAY_INNER
 #define FLX_STAY_INNER 12
+#endif
+// Ray batches (k_trace_batch / k_any_batch: cheap load / store bodies, incoherent rays of very different lengths) take
+// their own set through Job::BATCH; tuned on cfg5 with tools/tune_batch.sh: refilling at 8 free lanes instead of 16
+// is +5 % there (2 610 -> 2 740 Mrays/s: the retire body of a batch is two loads and two stores), 4 the same, 24 is -17 %;
+// the other three thresholds sit on a plateau (23 settings within 3 %).
+#ifndef FLX_VOTE_RETIRE_BATCH
+#define FLX_VOTE_RETIRE_BATCH 8
+#endif
+#ifndef FLX_VOTE_LEAF_BATCH
+#define FLX_VOTE_LEAF_BATCH FLX_VOTE_LEAF
+#endif
+#ifndef FLX_STAY_LEAF_BATCH
+#define FLX_STAY_LEAF_BATCH FLX_STAY_LEAF
+#endif
+#ifndef FLX_STAY_INNER_BATCH
+#define FLX_STAY_INNER_BATCH FLX_STAY_INNER
 #endif
 // any-hit rays (shorter traversals, early exit) may take their own thresholds; default: the same
 #ifndef FLX_VOTE_RETIRE_ANY
@@ -183,8 +200,11 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
 {
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
-    constexpr int VOTE_RETIRE = ANY ? FLX_VOTE_RETIRE_ANY : FLX_VOTE_RETIRE, VOTE_LEAF = ANY ? FLX_VOTE_LEAF_ANY : FLX_VOTE_LEAF;
-    constexpr int STAY_LEAF = ANY ? FLX_STAY_LEAF_ANY : FLX_STAY_LEAF, STAY_INNER = ANY ? FLX_STAY_INNER_ANY : FLX_STAY_INNER;
+    constexpr bool BATCH = Job::BATCH;
+    constexpr int VOTE_RETIRE = BATCH ? FLX_VOTE_RETIRE_BATCH : (ANY ? FLX_VOTE_RETIRE_ANY : FLX_VOTE_RETIRE);
+    constexpr int VOTE_LEAF = BATCH ? FLX_VOTE_LEAF_BATCH : (ANY ? FLX_VOTE_LEAF_ANY : FLX_VOTE_LEAF);
+    constexpr int STAY_LEAF = BATCH ? FLX_STAY_LEAF_BATCH : (ANY ? FLX_STAY_LEAF_ANY : FLX_STAY_LEAF);
+    constexpr int STAY_INNER = BATCH ? FLX_STAY_INNER_BATCH : (ANY ? FLX_STAY_INNER_ANY : FLX_STAY_INNER);
     int stack[FLX_STACK_SIZE];
     int sp = 0, cur = FLX_TRAV_DONE;
     bool active = false, poolEmpty = false;

@@ -193,7 +193,7 @@ int flx_launch_reset(flx_ctx *ctx);
 int flx_launch_raygen(flx_ctx *ctx);
 int flx_launch_logic(flx_ctx *ctx, int firstIteration);
 int flx_launch_logic_regen(flx_ctx *ctx);
-int flx_launch_materials(flx_ctx *ctx);
+int flx_launch_materials(flx_ctx *ctx, bool renderEntry = false); // renderEntry: flx_render's iteration (always per-BxDF queues)
 int flx_launch_postprocess(flx_ctx *ctx);
 int flx_launch_bookkeeping(flx_ctx *ctx); // counters -> totals, pixel cursor advance, clear
 int flx_launch_advance_pixel(flx_ctx *ctx, uint32_t numPixels, uint32_t numNew);

@@ -28,7 +28,10 @@ FLX_DEV uint32_t warpPush(uint32_t *counter, bool pred) // see flx_wavefront.cu
 }
 
 // material type -> queue (wf_logic.cl:352-407); MIXED goes with diffuse
-FLX_DEV int materialQueueOf(int type, bool separate)
+// separate: 0 = single queue, 1 = the reference's separate queues (an unknown type falls into `default:` and the path
+// is dropped, wf_logic.cl:399-401), 2 = the render entry's internal per-BxDF compaction of single-queue mode (an
+// unknown type is shaded to zero by the diffuse body, exactly what wf_mat_all does with it)
+FLX_DEV int materialQueueOf(int type, uint32_t separate)
 {
     if (!separate) return FLX_Q_DIFFUSE; // -DWF_SINGLE_MAT_QUEUE
     switch (type)
@@ -40,7 +43,7 @@ FLX_DEV int materialQueueOf(int type, bool separate)
     case FLX_BXDF_IDEAL_REFLECTION: case FLX_BXDF_IDEAL_DIELECTRIC: return FLX_Q_DELTA;
     case FLX_BXDF_EMISSIVE: return FLX_Q_EMISSIVE;
     }
-    return -1;
+    return separate == 2u ? FLX_Q_DIFFUSE : -1;
 }
 
 static __host__ __device__ __forceinline__ uint32_t *counterOf(flx_queue_counters *c, int q) { return ((uint32_t *)c) + q; } // same order as FLX_Q_*
@@ -61,7 +64,7 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
     const uint32_t rounded = (maxId + FLX_WF_THREADS - 1u) & ~(uint32_t)(FLX_WF_THREADS - 1u); // whole CTAs: the push below has barriers
     const bool checkSpp = params.maxSpp > 0u; // -DCHECK_SPP
     __shared__ uint32_t sPush[FLX_WF_THREADS / 32][16]; // per warp: slot counts, then slot bases, of the ten counters
-    const bool separate = params.wfSeparateQueues != 0u;
+    const uint32_t separate = params.wfSeparateQueues; // 0 / 1, or 2 from the render entry (see materialQueueOf)
     const uint32_t cursor = REGEN ? *currPixelIdx : 0u;
 
     for (uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x; gid < rounded; gid += gridDim.x * blockDim.x)
@@ -308,6 +311,38 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
 // TYPES is the compile-time set of BxDFs this instantiation can meet in its queue.  Called by whole warps:
 // lane `k` of the queue (k may run past qlen in the last warp), then one aggregated push of the survivors.
 template <int TYPES>
+FLX_DEV void materialShade(const PathState &st, uint32_t gid, const MaterialsDev &md)
+{
+    const float4 thr = st.thr[gid], r1 = st.ray1[gid], h0 = st.hit0[gid], h1 = st.hit1[gid], h2 = st.hit2[gid];
+    uint32_t seed = __float_as_uint(thr.w);
+    SurfHit hit; hit.N = mk3(h1); hit.uvx = h2.x; hit.uvy = h2.y;
+    const Mat mat = loadMat(md.materials + __float_as_int(h2.z));
+    const bool backface = (st.logicFlags[gid] & 1u) != 0u;
+    const f3 dirIn = mk3(r1);
+    const f3 L = mk3(st.shw1[gid]);
+
+    const f3 bsdfNEE = bxdfEval<TYPES>(hit, mat, backface, md, dirIn, L);
+    const float bsdfPdfW = fmaxf(0.0f, bxdfPdf<TYPES>(hit, mat, backface, md, dirIn, L));
+
+    float pdfW = 0.0f;     // the reference leaves these unset for emissive / rejected glossy
+    f3 newDir = mk3(0.0f); // samples; the oracle pins them to 0 and so do we
+    const f3 bsdf = bxdfSample<TYPES>(hit, mat, backface, md, dirIn, newDir, pdfW, seed);
+
+    const f3 oldT = mk3(thr);
+    f3 newT;
+    if (pdfW == 0.0f || isZero(bsdf)) newT = mk3(0.0f);
+    else newT = oldT * bsdf * dot(hit.N, newDir) / pdfW;
+    const f3 orig = mk3(h0) + 1e-4f * newDir;
+
+    st.nee1[gid] = mk4(bsdfNEE, bsdfPdfW);
+    st.nee2[gid] = mk4(oldT, 0.0f);
+    st.thr[gid] = mk4u(newT, seed);
+    st.ray0[gid] = mk4(orig, pdfW);
+    st.ray1[gid] = make_float4(newDir.x, newDir.y, newDir.z, r1.w);
+    st.lastSpecular[gid] = FLX_BXDF_IS_SINGULAR(mat.type) ? 1u : 0u;
+}
+
+template <int TYPES>
 FLX_DEV void materialBody(const PathState &st, const uint32_t *__restrict__ queue, uint32_t qlen, uint32_t k,
                           uint32_t *__restrict__ extQueue, uint32_t *extCounter, const MaterialsDev &md)
 {
@@ -316,33 +351,7 @@ FLX_DEV void materialBody(const PathState &st, const uint32_t *__restrict__ queu
     if (valid)
     {
         gid = queue[k];
-        const float4 thr = st.thr[gid], r1 = st.ray1[gid], h0 = st.hit0[gid], h1 = st.hit1[gid], h2 = st.hit2[gid];
-        uint32_t seed = __float_as_uint(thr.w);
-        SurfHit hit; hit.N = mk3(h1); hit.uvx = h2.x; hit.uvy = h2.y;
-        const Mat mat = loadMat(md.materials + __float_as_int(h2.z));
-        const bool backface = (st.logicFlags[gid] & 1u) != 0u;
-        const f3 dirIn = mk3(r1);
-        const f3 L = mk3(st.shw1[gid]);
-
-        const f3 bsdfNEE = bxdfEval<TYPES>(hit, mat, backface, md, dirIn, L);
-        const float bsdfPdfW = fmaxf(0.0f, bxdfPdf<TYPES>(hit, mat, backface, md, dirIn, L));
-
-        float pdfW = 0.0f;     // the reference leaves these unset for emissive / rejected glossy
-        f3 newDir = mk3(0.0f); // samples; the oracle pins them to 0 and so do we
-        const f3 bsdf = bxdfSample<TYPES>(hit, mat, backface, md, dirIn, newDir, pdfW, seed);
-
-        const f3 oldT = mk3(thr);
-        f3 newT;
-        if (pdfW == 0.0f || isZero(bsdf)) newT = mk3(0.0f);
-        else newT = oldT * bsdf * dot(hit.N, newDir) / pdfW;
-        const f3 orig = mk3(h0) + 1e-4f * newDir;
-
-        st.nee1[gid] = mk4(bsdfNEE, bsdfPdfW);
-        st.nee2[gid] = mk4(oldT, 0.0f);
-        st.thr[gid] = mk4u(newT, seed);
-        st.ray0[gid] = mk4(orig, pdfW);
-        st.ray1[gid] = make_float4(newDir.x, newDir.y, newDir.z, r1.w);
-        st.lastSpecular[gid] = FLX_BXDF_IS_SINGULAR(mat.type) ? 1u : 0u;
+        materialShade<TYPES>(st, gid, md);
     }
     const uint32_t slot = warpPush(extCounter, valid);
     if (valid) extQueue[slot] = gid;
@@ -364,34 +373,54 @@ k_material(PathState st, const uint32_t *__restrict__ queue, const uint32_t *__r
 // queues are laid end to end in units of 32-path chunks and every warp takes chunks round robin, running the
 // specialised body of the queue its chunk belongs to.  Most queues are short (a few thousand paths), so six
 // launches spend their time ramping up and draining; together they fill the machine once.
+// Extension-queue slots without atomics: every shaded path continues with exactly one extension ray
+// (wf_mat_diffuse.cl:60-65), so path k of queue i owns slot extBefore + len(queues before i) + k, where extBefore
+// is the counter as the logic stage left it.  The counter itself is advanced once, by the CTA that finishes last
+// (every other CTA has read extBefore by then) — the reference's one atomic per path, and the one per warp of the
+// first version here (15 % of this kernel's stall samples: they all hit one L2 word), are gone.
 __global__ void __launch_bounds__(FLX_WF_THREADS, FLX_MAT_MIN_BLOCKS)
-k_materials_separate(PathState st, Queues qs, uint32_t N, MaterialsDev md)
+k_materials_separate(PathState st, Queues qs, uint32_t N, MaterialsDev md, unsigned int *arrive)
 {
     const uint32_t *cnt = (const uint32_t *)qs.counters; // word q = length of queue q
-    uint32_t end[6];                                      // chunk index one past queue FLX_Q_DIFFUSE + i
-    uint32_t acc = 0u;
+    const uint32_t extBefore = cnt[FLX_Q_EXTENSION];
+    uint32_t end[6], pre[6];                              // chunk index one past queue FLX_Q_DIFFUSE + i; paths in the queues before it
+    uint32_t acc = 0u, total = 0u;
 #pragma unroll
-    for (int i = 0; i < 6; i++) { acc += (cnt[FLX_Q_DIFFUSE + i] + 31u) >> 5; end[i] = acc; }
+    for (int i = 0; i < 6; i++) { const uint32_t n = cnt[FLX_Q_DIFFUSE + i]; pre[i] = total; total += n; acc += (n + 31u) >> 5; end[i] = acc; }
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warpsTotal = (gridDim.x * blockDim.x) >> 5;
-    uint32_t *extQueue = qs.q[FLX_Q_EXTENSION], *extCounter = &qs.counters->extensionQueue;
+    uint32_t *extQueue = qs.q[FLX_Q_EXTENSION];
     for (uint32_t chunk = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; chunk < acc; chunk += warpsTotal)
     {
         int i = 0;
-        uint32_t first = 0u;
+        uint32_t first = 0u, before = 0u;
 #pragma unroll
-        for (int j = 0; j < 5; j++) if (chunk >= end[j]) { i = j + 1; first = end[j]; }
+        for (int j = 0; j < 5; j++) if (chunk >= end[j]) { i = j + 1; first = end[j]; before = pre[j + 1]; }
         const uint32_t k = ((chunk - first) << 5) + lane;
         const uint32_t *queue = qs.q[0] + (size_t)(FLX_Q_DIFFUSE + i) * N; // queues are contiguous, N apart
-        const uint32_t qlen = cnt[FLX_Q_DIFFUSE + i];
-        switch (i) // warp-uniform
+        if (k < cnt[FLX_Q_DIFFUSE + i])
         {
-        case 0: materialBody<FLX_BXDF_DIFFUSE>(st, queue, qlen, k, extQueue, extCounter, md); break;
-        case 1: materialBody<FLX_BXDF_GLOSSY>(st, queue, qlen, k, extQueue, extCounter, md); break;
-        case 2: materialBody<FLX_BXDF_GGX_ROUGH_REFLECTION>(st, queue, qlen, k, extQueue, extCounter, md); break;
-        case 3: materialBody<FLX_BXDF_GGX_ROUGH_DIELECTRIC>(st, queue, qlen, k, extQueue, extCounter, md); break;
-        case 4: materialBody<FLX_BXDF_IDEAL_REFLECTION | FLX_BXDF_IDEAL_DIELECTRIC>(st, queue, qlen, k, extQueue, extCounter, md); break;
-        default: materialBody<FLX_BXDF_EMISSIVE>(st, queue, qlen, k, extQueue, extCounter, md); break;
+            const uint32_t gid = queue[k];
+            switch (i) // warp-uniform
+            {
+            case 0: materialShade<FLX_BXDF_DIFFUSE>(st, gid, md); break;
+            case 1: materialShade<FLX_BXDF_GLOSSY>(st, gid, md); break;
+            case 2: materialShade<FLX_BXDF_GGX_ROUGH_REFLECTION>(st, gid, md); break;
+            case 3: materialShade<FLX_BXDF_GGX_ROUGH_DIELECTRIC>(st, gid, md); break;
+            case 4: materialShade<FLX_BXDF_IDEAL_REFLECTION | FLX_BXDF_IDEAL_DIELECTRIC>(st, gid, md); break;
+            default: materialShade<FLX_BXDF_EMISSIVE>(st, gid, md); break;
+            }
+            extQueue[extBefore + before + k] = gid;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0u)
+    {
+        __threadfence();
+        if (atomicAdd(arrive, 1u) == gridDim.x - 1u)
+        {
+            qs.counters->extensionQueue = extBefore + total;
+            *arrive = 0u;
         }
     }
 }
@@ -413,11 +442,26 @@ int flx_launch_logic(flx_ctx *ctx, int firstIteration)
     return FLX_OK;
 }
 
-// logic + raygen in one launch (the render entry's inner loop; the per-stage API keeps them apart)
+// logic + raygen in one launch (the render entry's inner loop; the per-stage API keeps them apart).
+// The render entry always compacts into the per-BxDF queues, whatever params.wfSeparateQueues says: which queue a
+// path waits in between two kernels is invisible from outside flx_render (the host sees totals, not queues), every
+// path is shaded by the same arithmetic either way (materialBody<TYPES> is wf_mat_all's body minus the branches a
+// queue cannot meet), and the reference's default single queue (useSeparateQueues = false, src/settings.cpp:31) costs
+// 4x in the material stage on a GPU because every warp then walks through all BxDF branches.  The per-stage calls
+// (flx_wf_logic / flx_wf_materials) honour the flag: the lock-step parity tests compare the queues themselves.
+static inline flx_render_params renderEntryParams(const flx_ctx *ctx)
+{
+    flx_render_params p = ctx->params;
+#ifndef FLX_RENDER_SINGLE_QUEUE_AS_IS
+    p.wfSeparateQueues = p.wfSeparateQueues ? 1u : 2u;
+#endif
+    return p;
+}
+
 int flx_launch_logic_regen(flx_ctx *ctx)
 {
     k_logic<true><<<wfGrid(ctx, ctx->N), FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->fb, ctx->mats, ctx->env, ctx->N,
-        0u, ctx->denoiserAOV, ctx->dPixelIdx, ctx->tileRank, ctx->tileWorld, ctx->params);
+        0u, ctx->denoiserAOV, ctx->dPixelIdx, ctx->tileRank, ctx->tileWorld, renderEntryParams(ctx));
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
@@ -426,10 +470,10 @@ int flx_launch_logic_regen(flx_ctx *ctx)
                        FLX_BXDF_GGX_ROUGH_DIELECTRIC | FLX_BXDF_IDEAL_DIELECTRIC | FLX_BXDF_EMISSIVE)
 
 // CLContext::enqueueWfMaterialKernels (clcontext.cpp:816-831)
-int flx_launch_materials(flx_ctx *ctx)
+int flx_launch_materials(flx_ctx *ctx, bool renderEntry)
 {
     const int grid = wfGrid(ctx, ctx->N);
-    if (!ctx->params.wfSeparateQueues)
+    if (!(renderEntry ? renderEntryParams(ctx) : ctx->params).wfSeparateQueues)
     {
         k_material<FLX_ALL_TYPES><<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs.q[FLX_Q_DIFFUSE], counterOf(ctx->qs.counters, FLX_Q_DIFFUSE), ctx->qs.q[FLX_Q_EXTENSION], &ctx->qs.counters->extensionQueue, ctx->mats);
         FLX_LAUNCHED(ctx);
@@ -437,7 +481,7 @@ int flx_launch_materials(flx_ctx *ctx)
     }
     static_assert(FLX_Q_GLOSSY == FLX_Q_DIFFUSE + 1 && FLX_Q_GGX_REFL == FLX_Q_DIFFUSE + 2 && FLX_Q_GGX_REFR == FLX_Q_DIFFUSE + 3 &&
                   FLX_Q_DELTA == FLX_Q_DIFFUSE + 4 && FLX_Q_EMISSIVE == FLX_Q_DIFFUSE + 5, "material queues are consecutive");
-    k_materials_separate<<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->N, ctx->mats);
+    k_materials_separate<<<grid, FLX_WF_THREADS, 0, ctx->stream>>>(ctx->st, ctx->qs, ctx->N, ctx->mats, (unsigned int *)(ctx->dPixelIdx + 5)); // arrival word: zero at rest
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }

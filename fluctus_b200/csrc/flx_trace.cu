@@ -44,6 +44,7 @@ FLX_DEV AreaLightGeom makeLightGeom(const flx_area_light &al)
 // wf_extrays.cl:5-36
 struct ExtJob
 {
+    static constexpr bool BATCH = false;
     const DevBVH &bvh; const PathState &st; const uint32_t *queue; const flx_render_params &params;
     uint32_t gid; unsigned int nHits, nRays;
     uint32_t len; // pathLen, which travels in the .w lane of the direction: kept so that the store needs no read
@@ -80,6 +81,7 @@ struct ExtJob
 // wf_shadowrays.cl:6-39
 struct ShadowJob
 {
+    static constexpr bool BATCH = false;
     const PathState &st; const uint32_t *queue; const flx_render_params &params;
     uint32_t gid; unsigned int nHits, nRays;
     FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
@@ -107,6 +109,7 @@ struct ShadowJob
 // handling is ExtJob's (hit record + pathLen); the shading half of the stage runs in k_mk_vertex_shade.
 struct MkVertexJob
 {
+    static constexpr bool BATCH = false;
     ExtJob ext;
     FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
     {
@@ -124,6 +127,7 @@ struct MkVertexJob
 template <bool LIGHT>
 struct MkShadowJob
 {
+    static constexpr bool BATCH = false;
     const PathState &st; const flx_render_params &params;
     uint32_t gid;
     FLX_DEV bool load(unsigned int k, f3 &o, f3 &d, float &tmax)
@@ -146,6 +150,7 @@ struct MkShadowJob
 // the light quad as an implicit hit when sampleImpl && useAreaLight; result as a Hit record (geom.h:152-163)
 struct PickJob
 {
+    static constexpr bool BATCH = false;
     const DevBVH &bvh; const flx_render_params &params; float ndcX, ndcY; float4 *out;
     FLX_DEV bool load(unsigned int, f3 &o, f3 &d, float &tmax)
     {
@@ -183,6 +188,7 @@ struct PickJob
 // ray batch, closest hit: rays as 2 x float4 {o.xyz, tmax} {d.xyz, -}
 struct BatchJob
 {
+    static constexpr bool BATCH = true;
     const DevBVH &bvh; const float4 *rays; int32_t *hitI; float *hitT; float4 *hits;
     unsigned int k; unsigned int nHits, nRays;
     FLX_DEV bool load(unsigned int kk, f3 &o, f3 &d, float &tmax)
@@ -218,6 +224,7 @@ struct BatchJob
 
 struct AnyBatchJob
 {
+    static constexpr bool BATCH = true;
     const float4 *rays; uint8_t *occ;
     unsigned int k; unsigned int nHits, nRays;
     FLX_DEV bool load(unsigned int kk, f3 &o, f3 &d, float &tmax)
