@@ -118,11 +118,15 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
                 f3 bg = mk3(0.0f);
                 if (params.useEnvMap)
                 {
-                    if (len == 1u || params.sampleImpl) bg = evalEnvMapDir(env, rayDir) * params.envMapStrength;
-                    if (params.sampleImpl && params.sampleExpl && len > 1u && !lastSpecular)
+                    const bool wantBg = len == 1u || params.sampleImpl;
+                    const bool wantPdf = params.sampleImpl && params.sampleExpl && len > 1u && !lastSpecular;
+                    float u = 0.0f, v = 0.0f;
+                    if (wantBg || wantPdf) directionToUV(rayDir, u, v); // one atan2f + acosf for both look-ups
+                    if (wantBg) bg = envLinear(env, u, v) * params.envMapStrength;
+                    if (wantPdf)
                     {
                         const float lightPickProb = lastPickProb;
-                        const float directPdfW = envMapPdf(env, rayDir);
+                        const float directPdfW = envMapPdfUV(env, rayDir, u, v);
                         weight = (lastPdfW * lightPickProb) / (lastPdfW * lightPickProb + directPdfW);
                     }
                 }

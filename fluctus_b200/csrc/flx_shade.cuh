@@ -156,6 +156,15 @@ FLX_DEV f3 evalEnvMapDir(const EnvMapDev &e, f3 dir) // :35-39
     directionToUV(dir, u, v);
     return envLinear(e, u, v);
 }
+// :95-109 with the (u, v) of the direction supplied by the caller (same directionToUV, evaluated once when the
+// radiance and the pdf of one direction are both needed)
+FLX_DEV float envMapPdfUV(const EnvMapDev &e, f3 direction, float u, float v)
+{
+    if (direction.y > 0.99f) return 0.0f;
+    const int iu = min((int)floorf(u * (float)e.w), e.w - 1);
+    const int iv = min((int)floorf(v * (float)e.h), e.h - 1);
+    return __ldg(e.pdf + iv * e.w + iu) * rsqrt_(1.0f - direction.y * direction.y);
+}
 // :63-92 alias-method sample; three dependent table reads per sample
 FLX_DEV void sampleEnvMapAlias(float r, f3 &L, float &pdfW, const EnvMapDev &e)
 {
