@@ -4,7 +4,9 @@
 #include "flx_bxdf.cuh"
 #include "flx_raygen.cuh"
 
+#ifndef FLX_WF_THREADS
 #define FLX_WF_THREADS 256
+#endif
 #ifndef FLX_LOGIC_MIN_BLOCKS
 #define FLX_LOGIC_MIN_BLOCKS 4
 #endif
