@@ -45,6 +45,7 @@ WIDTH, HEIGHT = 1920, 1080
 # traversal launch ends with a tail in which a few long rays keep the GPU waiting, and a 4x larger pool amortises
 # it (measured: 2^20 145, 2^21 153, 2^22 157, 2^23 158 Msamples/s).  FLX_BENCH_TASKS overrides it for experiments.
 NUM_TASKS = int(os.environ.get("FLX_BENCH_TASKS", 1 << 22))
+BITSTACK = os.environ.get("FLX_BENCH_BITSTACK", "0") == "1"  # experiment switch: Settings::clUseBitstack traversal
 MAX_BOUNCES = 8
 ITERS_PER_STEP = 48          # wavefront iterations per frame
 CPU_TASKS = 1 << 18          # path pool of the CPU arm (throughput per path does not depend on it)
@@ -259,6 +260,7 @@ def run_raycast(dev, rank, world, teapot, peak_gbs, steps, warmup, check):
     stream = torch.cuda.current_stream(dev)
     ctx = CudaContext(num_tasks=1024, device=dev.index, stream=stream.cuda_stream)
     ctx.uploadSceneData(grid)
+    ctx.setTraversal(BITSTACK)
     t_build = time.perf_counter() - t_build
     d_rays = torch.from_numpy(rays).to(dev)
     d_i = torch.empty(n, dtype=torch.int32, device=dev)
@@ -355,6 +357,7 @@ def run_ours(args):
     tr = fx.Tracer(WIDTH, HEIGHT, num_tasks=NUM_TASKS, device=local, rank=rank, world_size=world,
                    stream=stream.cuda_stream, **settings)
     tr.init(scene, env)
+    tr.clctx.setTraversal(BITSTACK)
     c = tr.clctx
     pix = pixels_tensor(c, dev)
     cursor0 = tr._cursor_start()

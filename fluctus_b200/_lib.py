@@ -24,6 +24,7 @@ SIGNATURES = {
     "flx_update_params": (I32, [V, V]),
     "flx_set_options": (I32, [V, I32, U32]),
     "flx_set_pixel_sharding": (I32, [V, U32, U32]),
+    "flx_set_traversal": (I32, [V, I32]),
     "flx_reset_pixel_index": (I32, [V]),
     "flx_set_pixel_index": (I32, [V, U32]),
     "flx_update_pixel_index": (I32, [V, U32, U32]),

@@ -89,6 +89,10 @@ class CudaContext:
     def setOptions(self, denoiser_aov=False, seed_offset=0):
         self._check(self.L.flx_set_options(self.h, int(denoiser_aov), int(seed_offset)))
 
+    def setTraversal(self, use_bitstack):
+        """Settings::clUseBitstack: stackless bit-trail traversal (src/bvh.cl:12-230) instead of the 64-entry stack."""
+        self._check(self.L.flx_set_traversal(self.h, int(bool(use_bitstack))))
+
     def setPixelSharding(self, rank, world):
         """Preview sharding: this context traces only the image rows y % world == rank (world=1: off)."""
         self._check(self.L.flx_set_pixel_sharding(self.h, int(rank), int(world)))

@@ -4,7 +4,7 @@
 // flx_trace.cu re-packs them once per scene into three 16-byte-vectorised streams:
 //
 //   inner node  64 B = 4 x float4   {L.min.xyz L.max.x} {L.max.yz R.min.xy} {R.min.z R.max.xyz}
-//                                    {leftRef, rightRef, -, -}
+//                                    {leftRef, rightRef, parent, -}
 //       both children's boxes live in the parent, so one node visit is one 64-byte fetch instead
 //       of the reference's 48 B node + two 48 B child fetches (src/bvh.cl:250, :284-285).
 //       ref >= 0: index of an inner node in this array;  ref < 0: ~ref = first leaf slot.
@@ -46,6 +46,7 @@ FLX_DEV void stageTopNodes(const DevBVH &bvh, float4 *top)
 }
 
 #define FLX_STACK_SIZE 64 // reference: uint stack[64] (src/bvh.cl:240)
+#define FLX_BITSTACK_MAX_DEPTH 31 // -DUSE_BITSTACK keeps one flag per level in a 32-bit word (src/bvh.cl:14-15)
 
 // One 256-bit load (sm_100: LDG.E.256) = half an inner node.  Rays of a warp sit in different nodes, so every lane of
 // a load instruction costs the L1 its own tag look-up whatever the access width: fetching the 64-byte node with two
@@ -195,7 +196,56 @@ FLX_DEV void prefetchRef(const DevBVH &bvh, int ref)
     else asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 }
 
-template <bool ANY, bool COUNT, class Job>
+// How a ray remembers the far children it postponed — the two halves of src/bvh.cl.
+//   StackTrail: `uint stack[64]` of node references (src/bvh.cl:234-373, the reference's default).
+//   BitTrail:   -DUSE_BITSTACK (src/bvh.cl:12-230, Settings::clUseBitstack): no stack, two 32-bit trails — bit k of
+//               `lst` (`rst`) says "the right (left) sibling at level k is still to be visited" — and parent links to
+//               walk back up; depth <= 31.  Same visit order, same box tests (a postponed child is not re-tested), so
+//               the same hits bit for bit; what differs is the memory behaviour: no 256-byte local-memory stack per
+//               ray, but one 16-byte reference fetch per level climbed on the way back.
+// The inner-node record keeps the parent's index in its third reference word for the climb.
+// (The state of a trail is scalars only and the stack array lives beside it in traceLoop: an array inside the struct
+// keeps the whole struct — the stack pointer included — in local memory.)
+struct StackTrail
+{
+    enum { SLOTS = FLX_STACK_SIZE };
+    int sp;
+    FLX_DEV void reset() { sp = 0; }
+    FLX_DEV void both(int *stack, int, bool, int far) { stack[sp++] = far; } // node, left child first?, postponed child
+    FLX_DEV void one(int) {}
+    FLX_DEV int back(const int *stack, const DevBVH &, const float4 *) { return sp ? stack[--sp] : FLX_TRAV_DONE; }
+};
+struct BitTrail
+{
+    enum { SLOTS = 1 };
+    unsigned lst, rst;
+    int par; // inner node the current node was entered from
+    FLX_DEV void reset() { lst = 0u; rst = 0u; par = -1; }
+    FLX_DEV void both(int *, int node, bool leftFirst, int) // src/bvh.cl:61-76
+    {
+        if (leftFirst) { lst = (lst | 1u) << 1; rst <<= 1; }
+        else { rst = (rst | 1u) << 1; lst <<= 1; }
+        par = node;
+    }
+    FLX_DEV void one(int node) { lst <<= 1; rst <<= 1; par = node; } // :77-88
+    FLX_DEV int back(const int *, const DevBVH &bvh, const float4 *top) // the trackback loop, :95-124
+    {
+        if ((lst | rst) == 0u) return FLX_TRAV_DONE;
+        int t = par; // first turn of the reference's loop: the flags of the current level are clear, step to the parent
+        lst >>= 1; rst >>= 1;
+        while ((lst | rst) != 0u)
+        {
+            const float4 n3 = t < bvh.topN ? top[3 * FLX_TOP_NODES + t] : __ldg(bvh.nodes + 4 * (size_t)t + 3);
+            if (lst & 1u) { lst = (lst & ~1u) << 1; rst <<= 1; par = t; return __float_as_int(n3.y); } // right sibling is due
+            if (rst & 1u) { rst = (rst & ~1u) << 1; lst <<= 1; par = t; return __float_as_int(n3.x); } // left sibling is due
+            t = __float_as_int(n3.z);
+            lst >>= 1; rst >>= 1;
+        }
+        return FLX_TRAV_DONE;
+    }
+};
+
+template <bool ANY, bool COUNT, class Trail, class Job>
 FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &job, unsigned int *cursor, unsigned int total, TravCount &cnt)
 {
     const unsigned FULL = 0xffffffffu;
@@ -205,8 +255,9 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
     constexpr int VOTE_LEAF = BATCH ? FLX_VOTE_LEAF_BATCH : (ANY ? FLX_VOTE_LEAF_ANY : FLX_VOTE_LEAF);
     constexpr int STAY_LEAF = BATCH ? FLX_STAY_LEAF_BATCH : (ANY ? FLX_STAY_LEAF_ANY : FLX_STAY_LEAF);
     constexpr int STAY_INNER = BATCH ? FLX_STAY_INNER_BATCH : (ANY ? FLX_STAY_INNER_ANY : FLX_STAY_INNER);
-    int stack[FLX_STACK_SIZE];
-    int sp = 0, cur = FLX_TRAV_DONE;
+    Trail trail; trail.reset();
+    int stack[Trail::SLOTS];
+    int cur = FLX_TRAV_DONE;
     bool active = false, poolEmpty = false;
     f3 o = mk3(0.0f), d = mk3(0.0f), dinv = mk3(0.0f);
     RayHit best; best.t = 0.0f; best.u = 0.0f; best.v = 0.0f; best.slot = -1;
@@ -242,7 +293,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                         {
                             dinv = mk3(recip(d.x), recip(d.y), recip(d.z));
                             best.t = tmax; best.u = 0.0f; best.v = 0.0f; best.slot = -1;
-                            cur = bvh.rootRef; sp = 0; active = true;
+                            cur = bvh.rootRef; trail.reset(); active = true;
                         }
                     }
                 }
@@ -272,7 +323,7 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                         found = true;
                     }
                     if (ANY && found) cur = FLX_TRAV_DONE;
-                    else if (__float_as_int(q1.w) != 0) cur = sp ? stack[--sp] : FLX_TRAV_DONE; // last slot of the leaf
+                    else if (__float_as_int(q1.w) != 0) cur = trail.back(stack, bvh, top); // last slot of the leaf
                     else cur = cur - 1;                                                         // ~(slot + 1)
                     prefetchRef<FLX_PF_CUR>(bvh, cur);
                 }
@@ -310,13 +361,13 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                     {
                         const bool swap = rnear < lnear; // left first on equal entry distance (src/bvh.cl:293-300)
                         const int far = swap ? l : r;
-                        stack[sp++] = far;
+                        trail.both(stack, cur, !swap, far);
                         cur = swap ? r : l;
                         if (!ANY) prefetchRef<FLX_PF_PUSH>(bvh, far);
                     }
-                    else if (lh) cur = l;
-                    else if (rh) cur = r;
-                    else cur = sp ? stack[--sp] : FLX_TRAV_DONE;
+                    else if (lh) { trail.one(cur); cur = l; }
+                    else if (rh) { trail.one(cur); cur = r; }
+                    else cur = trail.back(stack, bvh, top);
                     if (COUNT && cur < 0 && cur != FLX_TRAV_DONE) cnt.leaf++;
                     prefetchRef<FLX_PF_CUR>(bvh, cur);
                 }

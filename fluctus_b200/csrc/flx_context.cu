@@ -265,6 +265,18 @@ int flx_set_options(flx_ctx *ctx, int denoiser_aov, uint32_t seed_offset)
     return FLX_OK;
 }
 
+// Settings::clUseBitstack -> -DUSE_BITSTACK (src/settings.cpp:27, src/clcontext.cpp:145-155): which half of src/bvh.cl walks the tree
+int flx_set_traversal(flx_ctx *ctx, int use_bitstack)
+{
+    FLX_CHECK_CTX(ctx);
+    const bool want = use_bitstack != 0;
+    if (want && ctx->sceneReady && ctx->treeDepth > FLX_BITSTACK_MAX_DEPTH)
+        return flx_fail(ctx, FLX_ERR_ARG, "flx_set_traversal: the uploaded hierarchy is deeper than the 31 levels the bit-stack traversal can track");
+    if (want != ctx->useBitstack) invalidateGraph(ctx);
+    ctx->useBitstack = want;
+    return FLX_OK;
+}
+
 int flx_set_pixel_sharding(flx_ctx *ctx, uint32_t rank, uint32_t world)
 {
     FLX_CHECK_CTX(ctx);

@@ -120,6 +120,7 @@ struct flx_ctx
     flx_triangle *dTris160 = nullptr;
     float *dGammaLut = nullptr;
     bool sceneReady = false;
+    bool useBitstack = false; uint32_t treeDepth = 0; // Settings::clUseBitstack (flx_set_traversal); depth of the uploaded hierarchy
     bool traceSetupDone = false; // cudaFuncSetAttribute(MaxDynamicSharedMemorySize) done on this device
     EnvMapDev env{}; float4 *dEnv = nullptr; float *dProb = nullptr, *dPdf = nullptr; int *dAlias = nullptr;
 

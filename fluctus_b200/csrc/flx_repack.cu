@@ -60,6 +60,9 @@ int flx_repack_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, cons
             todo.push_back(std::make_pair((uint32_t)ri, it.second + 1));
         }
         if (maxDepth > FLX_STACK_SIZE) return flx_fail(ctx, FLX_ERR_ARG, "flx_upload_scene: hierarchy deeper than the 64-entry traversal stack");
+        if (ctx->useBitstack && maxDepth > FLX_BITSTACK_MAX_DEPTH)
+            return flx_fail(ctx, FLX_ERR_ARG, "flx_upload_scene: hierarchy deeper than the 31 levels the bit-stack traversal can track (flx_set_traversal)");
+        ctx->treeDepth = maxDepth;
     }
 
     auto refOf = [&](size_t child) -> int32_t {
@@ -83,7 +86,7 @@ int flx_repack_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, cons
             o[0] = make_float4(L.bmin.x, L.bmin.y, L.bmin.z, L.bmax.x);
             o[1] = make_float4(L.bmax.y, L.bmax.z, R.bmin.x, R.bmin.y);
             o[2] = make_float4(R.bmin.z, R.bmax.x, R.bmax.y, R.bmax.z);
-            int32_t refs[4] = {refOf(li), refOf(ri), 0, 0};
+            int32_t refs[4] = {refOf(li), refOf(ri), -1, 0}; // [2] = parent (inner index), filled in below
             memcpy(&o[3], refs, 16);
         }
         else
@@ -108,6 +111,14 @@ int flx_repack_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, cons
                 o[2] = make_float4(e2x, e2y, e2z, 0.f); memcpy(&o[2].w, &t.matId, 4);
             }
         }
+    }
+    // parent links for the bit-stack traversal's climb (src/bvh.cl:121: top = n.parent)
+    for (size_t i = 0; i < n_nodes; i++)
+    {
+        if (nodes[i].nPrims != 0) continue;
+        const size_t kids[2] = {i + 1, (size_t)nodes[i].iStartOrRight};
+        for (size_t c : kids)
+            if (nodes[c].nPrims == 0) memcpy(&hNodes[4 * (size_t)innerIndex[c] + 3].z, &innerIndex[i], 4);
     }
     // uncovered slots (never referenced) still get a terminator so a stray read cannot run away
     for (size_t k = 0; k < n_indices; k++)

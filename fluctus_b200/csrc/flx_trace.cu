@@ -14,6 +14,9 @@
 #define FLX_TRACE_MIN_BLOCKS 1
 #endif
 
+template <bool BITS> struct TrailOf { typedef StackTrail type; };
+template <> struct TrailOf<true> { typedef BitTrail type; };
+
 FLX_DEV void flushCounts(unsigned long long *stats, const TravCount &c, unsigned int hits, unsigned int rays)
 {
     unsigned int v[5] = {c.inner, c.leaf, c.tri, hits, rays};
@@ -241,7 +244,8 @@ struct AnyBatchJob
     }
 };
 
-template <bool COUNT>
+// BITS selects the trail (flx_bvh.cuh): false = the reference's stack, true = its -DUSE_BITSTACK traversal
+template <bool COUNT, bool BITS>
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
       unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
@@ -252,11 +256,11 @@ k_ext(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_qu
     stageTopNodes(bvh, topNodes);
     ExtJob job = {bvh, st, queue, params, 0u, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<false, COUNT>(bvh, topNodes, job, cursor, total, cnt);
+    traceLoop<false, COUNT, typename TrailOf<BITS>::type>(bvh, topNodes, job, cursor, total, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
-template <bool COUNT>
+template <bool COUNT, bool BITS>
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx_queue_counters *__restrict__ counters,
          unsigned int *cursor, unsigned long long *stats, const __grid_constant__ flx_render_params params)
@@ -267,7 +271,7 @@ k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx
     stageTopNodes(bvh, topNodes);
     ShadowJob job = {st, queue, params, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<true, COUNT>(bvh, topNodes, job, cursor, total, cnt);
+    traceLoop<true, COUNT, typename TrailOf<BITS>::type>(bvh, topNodes, job, cursor, total, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
@@ -275,6 +279,7 @@ k_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ queue, const flx
 // independent (extension rays read ray0/ray1 and write the hit record, shadow rays read shw0/shw1 and write
 // shadowBlocked), so a warp that finds the extension pool empty moves straight on to the shadow pool instead of
 // idling until the slowest extension ray of the grid has finished; the top of the tree is staged once.
+template <bool BITS>
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_ext_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ extQueue, const uint32_t *__restrict__ shadowQueue,
              flx_queue_counters *counters, unsigned int *cursors, RenderTotals *totals, uint32_t *pixelIdx, uint32_t ownedPixels,
@@ -289,12 +294,12 @@ k_ext_shadow(DevBVH bvh, PathState st, const uint32_t *__restrict__ extQueue, co
         if (nExt)
         {
             ExtJob job = {bvh, st, extQueue, params, 0u, 0u, 0u, 0u};
-            traceLoop<false, false>(bvh, topNodes, job, cursors, nExt, cnt);
+            traceLoop<false, false, typename TrailOf<BITS>::type>(bvh, topNodes, job, cursors, nExt, cnt);
         }
         if (nShadow)
         {
             ShadowJob job = {st, shadowQueue, params, 0u, 0u, 0u};
-            traceLoop<true, false>(bvh, topNodes, job, cursors + 1, nShadow, cnt);
+            traceLoop<true, false, typename TrailOf<BITS>::type>(bvh, topNodes, job, cursors + 1, nShadow, cnt);
         }
     }
     // The CTA that finishes last closes the iteration: what the reference's host does between iterations
@@ -319,7 +324,7 @@ k_mk_vertex(DevBVH bvh, PathState st, unsigned int total, unsigned int *cursor, 
     stageTopNodes(bvh, topNodes);
     MkVertexJob job = {{bvh, st, nullptr, params, 0u, 0u, 0u, 0u}};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<false, false>(bvh, topNodes, job, cursor, total, cnt);
+    traceLoop<false, false, StackTrail>(bvh, topNodes, job, cursor, total, cnt);
 }
 
 template <bool LIGHT>
@@ -330,7 +335,7 @@ k_mk_shadow(DevBVH bvh, PathState st, unsigned int total, unsigned int *cursor, 
     stageTopNodes(bvh, topNodes);
     MkShadowJob<LIGHT> job = {st, params, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<true, false>(bvh, topNodes, job, cursor, total, cnt);
+    traceLoop<true, false, StackTrail>(bvh, topNodes, job, cursor, total, cnt);
 }
 
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
@@ -340,10 +345,10 @@ k_pick(DevBVH bvh, float ndcX, float ndcY, float4 *out, unsigned int *cursor, co
     stageTopNodes(bvh, topNodes);
     PickJob job = {bvh, params, ndcX, ndcY, out};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<false, false>(bvh, topNodes, job, cursor, 1u, cnt);
+    traceLoop<false, false, StackTrail>(bvh, topNodes, job, cursor, 1u, cnt);
 }
 
-template <bool COUNT>
+template <bool COUNT, bool BITS>
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
               int32_t *__restrict__ hitI, float *__restrict__ hitT, float4 *__restrict__ hits)
@@ -352,11 +357,11 @@ k_trace_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsig
     stageTopNodes(bvh, topNodes);
     BatchJob job = {bvh, rays, hitI, hitT, hits, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<false, COUNT>(bvh, topNodes, job, cursor, n, cnt);
+    traceLoop<false, COUNT, typename TrailOf<BITS>::type>(bvh, topNodes, job, cursor, n, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
-template <bool COUNT>
+template <bool COUNT, bool BITS>
 __global__ void __launch_bounds__(FLX_TRACE_THREADS, FLX_TRACE_MIN_BLOCKS)
 k_any_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigned int *cursor, unsigned long long *stats,
             uint8_t *__restrict__ occ)
@@ -365,7 +370,7 @@ k_any_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigne
     stageTopNodes(bvh, topNodes);
     AnyBatchJob job = {rays, occ, 0u, 0u, 0u};
     TravCount cnt = {0u, 0u, 0u};
-    traceLoop<true, COUNT>(bvh, topNodes, job, cursor, n, cnt);
+    traceLoop<true, COUNT, typename TrailOf<BITS>::type>(bvh, topNodes, job, cursor, n, cnt);
     if (COUNT) flushCounts(stats, cnt, job.nHits, job.nRays);
 }
 
@@ -382,9 +387,12 @@ static int traceGrid(const flx_ctx *ctx) { return ctx->numSMs * FLX_TRACE_CTAS_P
 static cudaError_t traceKernelSetup(flx_ctx *ctx)
 {
     if (ctx->traceSetupDone) return cudaSuccess;
-    const void *kernels[] = {(const void *)k_ext<false>, (const void *)k_ext<true>, (const void *)k_shadow<false>, (const void *)k_shadow<true>,
-                             (const void *)k_trace_batch<false>, (const void *)k_trace_batch<true>, (const void *)k_any_batch<false>, (const void *)k_any_batch<true>,
-                             (const void *)k_ext_shadow, (const void *)k_pick, (const void *)k_mk_vertex, (const void *)k_mk_shadow<false>, (const void *)k_mk_shadow<true>};
+    const void *kernels[] = {(const void *)k_ext<false, false>, (const void *)k_ext<true, false>, (const void *)k_ext<false, true>,
+                             (const void *)k_shadow<false, false>, (const void *)k_shadow<true, false>, (const void *)k_shadow<false, true>,
+                             (const void *)k_trace_batch<false, false>, (const void *)k_trace_batch<true, false>, (const void *)k_trace_batch<false, true>,
+                             (const void *)k_any_batch<false, false>, (const void *)k_any_batch<true, false>, (const void *)k_any_batch<false, true>,
+                             (const void *)k_ext_shadow<false>, (const void *)k_ext_shadow<true>,
+                             (const void *)k_pick, (const void *)k_mk_vertex, (const void *)k_mk_shadow<false>, (const void *)k_mk_shadow<true>};
     for (const void *k : kernels)
     {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, FLX_TOP_SMEM_BYTES);
@@ -404,10 +412,13 @@ int flx_launch_ext(flx_ctx *ctx)
     FLX_CUDA(ctx, traceKernelSetup(ctx));
     unsigned int *cur = workCursor(ctx, 0);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
+    // the counting variants (visit statistics under the reference's default order) always walk with the stack
     if (ctx->counting)
-        k_ext<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, ctx->dTraceStats, ctx->params);
+        k_ext<true, false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, ctx->dTraceStats, ctx->params);
+    else if (ctx->useBitstack)
+        k_ext<false, true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, nullptr, ctx->params);
     else
-        k_ext<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, nullptr, ctx->params);
+        k_ext<false, false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.counters, cur, nullptr, ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
@@ -422,8 +433,12 @@ int flx_reset_trace_cursors(flx_ctx *ctx)
 int flx_launch_ext_shadow(flx_ctx *ctx)
 {
     FLX_CUDA(ctx, traceKernelSetup(ctx));
-    k_ext_shadow<<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.q[FLX_Q_SHADOW],
-        ctx->qs.counters, workCursor(ctx, 0), ctx->dTotals, ctx->dPixelIdx, flx_owned_pixels(ctx), ctx->params);
+    if (ctx->useBitstack)
+        k_ext_shadow<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.q[FLX_Q_SHADOW],
+            ctx->qs.counters, workCursor(ctx, 0), ctx->dTotals, ctx->dPixelIdx, flx_owned_pixels(ctx), ctx->params);
+    else
+        k_ext_shadow<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_EXTENSION], ctx->qs.q[FLX_Q_SHADOW],
+            ctx->qs.counters, workCursor(ctx, 0), ctx->dTotals, ctx->dPixelIdx, flx_owned_pixels(ctx), ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
@@ -456,9 +471,11 @@ int flx_launch_shadow(flx_ctx *ctx)
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
-        k_shadow<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, ctx->dTraceStats + 5, ctx->params);
+        k_shadow<true, false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, ctx->dTraceStats + 5, ctx->params);
+    else if (ctx->useBitstack)
+        k_shadow<false, true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, nullptr, ctx->params);
     else
-        k_shadow<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, nullptr, ctx->params);
+        k_shadow<false, false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, ctx->st, ctx->qs.q[FLX_Q_SHADOW], ctx->qs.counters, cur, nullptr, ctx->params);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
@@ -471,9 +488,11 @@ int flx_launch_trace_batch(flx_ctx *ctx, const float4 *dRays, size_t n, int32_t 
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
-        k_trace_batch<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 10, dHitI, dHitT, (float4 *)dHits);
+        k_trace_batch<true, false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 10, dHitI, dHitT, (float4 *)dHits);
+    else if (ctx->useBitstack)
+        k_trace_batch<false, true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dHitI, dHitT, (float4 *)dHits);
     else
-        k_trace_batch<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dHitI, dHitT, (float4 *)dHits);
+        k_trace_batch<false, false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dHitI, dHitT, (float4 *)dHits);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }
@@ -497,9 +516,11 @@ int flx_launch_any_batch(flx_ctx *ctx, const float4 *dRays, size_t n, uint8_t *d
     unsigned int *cur = workCursor(ctx, 1);
     FLX_CUDA(ctx, cudaMemsetAsync(cur, 0, sizeof(unsigned int), ctx->stream));
     if (ctx->counting)
-        k_any_batch<true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 15, dOcc);
+        k_any_batch<true, false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, ctx->dTraceStats + 15, dOcc);
+    else if (ctx->useBitstack)
+        k_any_batch<false, true><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dOcc);
     else
-        k_any_batch<false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dOcc);
+        k_any_batch<false, false><<<traceGrid(ctx), FLX_TRACE_THREADS, FLX_TOP_SMEM_BYTES, ctx->stream>>>(ctx->bvh, dRays, (unsigned int)n, cur, nullptr, dOcc);
     FLX_LAUNCHED(ctx);
     return FLX_OK;
 }

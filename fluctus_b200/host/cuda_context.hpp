@@ -64,6 +64,7 @@ public:
     void updateParams(const RenderParams &params) { check(flx_update_params(ctx, &params)); lastParams = params; }
     void recompileKernels(bool /*setArgs*/) {}
     void setPixelSharding(uint32_t rank, uint32_t world) { check(flx_set_pixel_sharding(ctx, rank, world)); }
+    void setTraversal(bool useBitstack) { check(flx_set_traversal(ctx, useBitstack ? 1 : 0)); } // Settings::clUseBitstack
     void setOptions(bool denoiserAOV, uint32_t seedOffset) { check(flx_set_options(ctx, denoiserAOV ? 1 : 0, seedOffset)); }
 
     // ---- pixel cursor (src/clcontext.cpp:917-927) -------------------------------------------------

@@ -23,7 +23,7 @@ struct Settings
     float renderScale = 1.0f;
     int windowWidth = 640, windowHeight = 480;
     uint32_t wfBufferSize = 1u << 20;
-    bool useRussianRoulette = false, useSeparateQueues = false;
+    bool useRussianRoulette = false, useSeparateQueues = false, clUseBitstack = false;
     int maxPathDepth = 10;
     uint32_t maxSpp = 0, maxRenderTime = 0;
     bool sampleImplicit = true, sampleExplicit = true, useEnvMap = false, useAreaLight = true;
@@ -51,6 +51,7 @@ struct Settings
         if (find(obj, "wfBufferSize", s)) wfBufferSize = (uint32_t)std::stoul(s);
         if (find(obj, "useRussianRoulette", s)) useRussianRoulette = s == "true";
         if (find(obj, "useSeparateQueues", s)) useSeparateQueues = s == "true";
+        if (find(obj, "clUseBitstack", s)) clUseBitstack = s == "true";
         if (find(obj, "maxPathDepth", s)) maxPathDepth = std::stoi(s);
         if (find(obj, "maxSpp", s)) maxSpp = (uint32_t)std::stoul(s);
         if (find(obj, "maxRenderTime", s)) maxRenderTime = (uint32_t)std::stoul(s);
@@ -148,6 +149,7 @@ public:
         clctx.uploadSceneData(s.tris.data(), s.tris.size(), s.indices.data(), s.indices.size(), s.nodes.data(), s.nodes.size(),
                               s.materials.data(), s.materials.size(), s.textures.empty() ? nullptr : s.textures.data(), s.textures.size(),
                               s.texels.empty() ? nullptr : s.texels.data(), s.texels.size());
+        clctx.setTraversal(settings.clUseBitstack); // -DUSE_BITSTACK (src/clcontext.cpp:145-155)
         clctx.setOptions(false, (uint32_t)rank * clctx.getNumTasks()); // sample sharding: seeds of one worldSize*N-task run
         clctx.updateParams(params);
         iteration = 0;

@@ -132,6 +132,14 @@ int flx_read_pixels(flx_ctx *ctx, int which /* flx_buffer */, void *host_out, si
 void *flx_device_ptr(flx_ctx *ctx, int which /* flx_buffer */); /* for the per-frame all-reduce */
 int flx_pick(flx_ctx *ctx, float ndc_x, float ndc_y, flx_hit *out);
 
+/* ---- traversal variant: Settings::clUseBitstack / -DUSE_BITSTACK (settings.cpp:27, clcontext.cpp:145-155) -------
+ * 0 (default) = the 64-entry stack of bvh.cl:234-373; non-zero = the stackless bit-trail traversal of bvh.cl:12-230
+ * (two 32-bit trails + parent links).  Same visit order and box tests, hence the same hits bit for bit; applies to
+ * the wavefront ray stages, flx_render and the ray-batch entry points (the microkernel stages, flx_pick and the
+ * visit-counting variants keep the stack).  Fails for hierarchies deeper than 31 levels (the reference's variant
+ * silently breaks there); flx_upload_scene refuses such a hierarchy while the switch is on. */
+int flx_set_traversal(flx_ctx *ctx, int use_bitstack);
+
 /* ---- multi-GPU frame combine inside one process (new; SURVEY.md §8e — the reference is single-device) ---------
  * ctxs[0..n): contexts on different GPUs rendering sample shards of the same frame (same resolution, seeds offset
  * with flx_set_options).  Drains their streams, then sums the accumulation buffers (and the denoiser AOV sums when

@@ -164,6 +164,78 @@ def test_deep_chain_hierarchy(ctx, oracle, teapot):
     ctx.uploadSceneData(teapot)
 
 
+def test_bitstack_traversal_matches_stack_and_oracle(oracle, teapot):
+    """Settings::clUseBitstack / -DUSE_BITSTACK (src/bvh.cl:12-230): the stackless bit-trail traversal gives the same
+    closest hit (index, distance, attributes) and the same occlusion flags as the stack traversal and as the oracle's
+    restatement of BOTH halves of bvh.cl — on the teapot, two reference assets, a replicated grid (depth 25), rays
+    starting inside, axis-parallel rays, finite tmax, a single-leaf scene and a depth-31 chain; deeper hierarchies are
+    refused while the switch is on."""
+    from fluctus_b200 import CudaContext, FluctusError, scene as fs
+    c = CudaContext(num_tasks=4096)
+    try:
+        c.setTraversal(True)
+        scenes = [("teapot", teapot), ("egyptcat", cached_scene("egyptcat")), ("psor_cube", cached_scene("psor_cube")),
+                  ("grid", fs.replicate_grid(teapot, (4, 3, 3), (2.2, 1.1, 1.4))), ("chain30", _chain_scene(teapot, 30))]
+        from fluctus_b200.abi import NODE_DT
+        tris = teapot["tris"][:5].copy()
+        node = np.zeros(1, NODE_DT)
+        pts = tris["v"][:, :, 0, :3].reshape(-1, 3)
+        node["bmin"][0, :3], node["bmax"][0, :3] = pts.min(0), pts.max(0)
+        node["parent"], node["iStartOrRight"], node["nPrims"] = -1, 0, 5
+        single = dict(teapot, tris=tris, nodes=node, indices=np.arange(5, dtype=np.uint32))
+        single["bounds"] = np.stack([pts.min(0), pts.max(0)])
+        scenes.append(("single_leaf", single))
+        for name, scene in scenes:
+            rays = np.concatenate([fs.bench_rays(1 << 15, scene["bounds"]), _rays_inside(scene, 1 << 14, 3)])
+            ax = _rays_inside(scene, 3072, 5)
+            ax[:1024, 4:7] = (1, 0, 0); ax[1024:2048, 4:7] = (0, -1, 0); ax[2048:, 4:7] = (0, 0, 1)
+            rays = np.concatenate([rays, ax])
+            rays[::7, 3] = np.float32(1.5)  # finite tmax on some
+            c.setTraversal(True)
+            c.uploadSceneData(scene)
+            bi, bt, bh = c.traceClosest(rays, want_hits=True)
+            bo = c.traceAny(rays)
+            c.setTraversal(False)
+            si, st_, sh = c.traceClosest(rays, want_hits=True)
+            so = c.traceAny(rays)
+            assert np.array_equal(bi, si) and np.array_equal(bits(bt), bits(st_)), name
+            assert bh.tobytes() == sh.tobytes() and np.array_equal(bo, so), name
+            for mode in (0, 1):  # the oracle's stack and bit-stack restatements
+                ref = oracle.trace_closest(scene, rays, mode)
+                assert np.array_equal(bi, ref["hit_i"]) and np.array_equal(bits(bt), bits(ref["hit_t"])), (name, mode)
+                assert np.array_equal(bo, oracle.trace_any(scene, rays, mode)), (name, mode)
+        # depth 32 = one level more than the trails can hold
+        c.setTraversal(True)
+        with pytest.raises(FluctusError) as e:
+            c.uploadSceneData(_chain_scene(teapot, 31))
+        assert "31 levels" in str(e.value)
+        c.setTraversal(False)
+        c.uploadSceneData(_chain_scene(teapot, 31))
+        with pytest.raises(FluctusError):
+            c.setTraversal(True)
+    finally:
+        c.close()
+
+
+def test_bitstack_render_agrees_with_stack_render(teapot, night_env):
+    """The wavefront render through flx_render with the bit-stack traversal: same ray / sample statistics and the same
+    image (up to the order of the float atomics) as with the stack."""
+    from fluctus_b200 import Tracer
+    out = []
+    for bitstack in (False, True):
+        tr = Tracer(96, 64, num_tasks=8192, max_bounces=4, use_env_map=True, use_area_light=True)
+        tr.init(teapot, night_env)
+        tr.clctx.setTraversal(bitstack)
+        tot = tr.render(iterations=120)
+        px = tr.pixels()
+        out.append((tot, px[..., :3].sum((0, 1)) / max(px[..., 3].sum(), 1)))
+        tr.close()
+    for k in ("primary", "extension", "shadow", "samples"):
+        # the same hits for every ray; which pixel a restarted path takes depends on the order of the queue atomics
+        assert abs(out[0][0][k] - out[1][0][k]) <= 0.02 * out[0][0][k], k
+    assert np.allclose(out[0][1], out[1][1], rtol=0.03)
+
+
 def test_host_batch_pipeline_chunk_boundaries(ctx, oracle, teapot):
     """flx_trace_closest / flx_trace_any with host buffers run as an upload / traverse / download pipeline over chunks of
     2^20 rays: a batch that ends 777 rays into its third chunk (and pageable, not pinned, memory) must give what one
