@@ -236,6 +236,55 @@ def test_bitstack_render_agrees_with_stack_render(teapot, night_env):
     assert np.allclose(out[0][1], out[1][1], rtol=0.03)
 
 
+def _twin_scene(teapot):
+    """Two coincident copies of the teapot under one root whose children have IDENTICAL boxes.  The left child (visited
+    first on equal entry distance, src/bvh.cl:293-300) owns the triangles [n, 2n) and the second half of the index
+    list, the right child the triangles [0, n): every hit has an exact-`t` twin, the traversal must report the left
+    copy (strictly-closer wins, so the twin met later does not replace it) while a loop over the triangle array in
+    index order reports the right copy."""
+    from fluctus_b200.abi import NODE_DT
+    A, B = teapot["nodes"].copy(), teapot["nodes"].copy()
+    nA, nT, nI = len(A), len(teapot["tris"]), len(teapot["indices"])
+    for half, node_off, idx_off in ((A, 1, nI), (B, 1 + nA, 0)):
+        inner = half["nPrims"] == 0
+        half["iStartOrRight"][inner] += node_off
+        half["iStartOrRight"][~inner] += idx_off
+        half["parent"][1:] += node_off
+        half["parent"][0] = 0
+    root = np.zeros(1, NODE_DT)
+    root["bmin"], root["bmax"] = teapot["nodes"]["bmin"][0], teapot["nodes"]["bmax"][0]
+    root["parent"], root["iStartOrRight"], root["nPrims"] = -1, 1 + nA, 0
+    scene = dict(teapot, nodes=np.concatenate([root, A, B]), tris=np.concatenate([teapot["tris"], teapot["tris"]]),
+                 indices=np.concatenate([teapot["indices"], teapot["indices"] + np.uint32(nT)]))
+    return scene
+
+
+def test_exact_ties_follow_the_reference_visit_order(oracle, teapot):
+    """Exact-`t` ties (coincident triangles in different subtrees): the reported index is decided by the visit order
+    and the strictly-closer rule, and must be the oracle's for every ray — with the stack and with the bit-stack."""
+    from fluctus_b200 import CudaContext, scene as fs
+    scene = _twin_scene(teapot)
+    n = len(teapot["tris"])
+    rays = np.concatenate([fs.bench_rays(1 << 16, scene["bounds"]), _rays_inside(scene, 1 << 15, 2)])
+    ref = oracle.trace_closest(scene, rays, 0)
+    hit = ref["hit_i"] >= 0
+    assert hit.mean() > 0.2 and (ref["hit_i"][hit] >= n).all()              # the left copy wins every tie
+    brute = oracle.trace_closest(scene, rays[:8192], 2)
+    assert np.array_equal(bits(brute["hit_t"]), bits(ref["hit_t"][:8192]))
+    assert (brute["hit_i"][hit[:8192]] < n).all()                           # index order would report the other copy
+    c = CudaContext(num_tasks=64)
+    try:
+        c.uploadSceneData(scene)
+        for bitstack in (False, True):
+            c.setTraversal(bitstack)
+            hit_i, hit_t, hits = c.traceClosest(rays, want_hits=True)
+            assert np.array_equal(hit_i, ref["hit_i"]) and np.array_equal(bits(hit_t), bits(ref["hit_t"])), bitstack
+            assert np.array_equal(hits["i"][hit], ref["hit_i"][hit])
+            assert np.array_equal(c.traceAny(rays) != 0, hit)
+    finally:
+        c.close()
+
+
 def test_host_batch_pipeline_chunk_boundaries(ctx, oracle, teapot):
     """flx_trace_closest / flx_trace_any with host buffers run as an upload / traverse / download pipeline over chunks of
     2^20 rays: a batch that ends 777 rays into its third chunk (and pageable, not pinned, memory) must give what one
