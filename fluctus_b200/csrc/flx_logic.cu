@@ -114,57 +114,26 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
             if (checkSpp && fb.spp[pixIdx] >= params.maxSpp) { terminate = true; maxSamplesReached = true; } // :76-84
             if (isZero(T) || lastPdfW == 0.0f) terminate = true;                                             // :87-88
 
-            if (hitI < 0 && !terminate) // escaped: implicit environment sample with MIS (:99-122)
+            const bool escaped = hitI < 0 && !terminate;                                        // :99
+            const bool lightHit = !escaped && params.useAreaLight && areaLightHit && !terminate; // :126
+            const bool survives = !terminate && !escaped && !lightHit;
+
+            // Environment look-ups.  A lane wants one either for an escaped ray (radiance and / or pdf of the ray's own
+            // direction, :99-122) or for the NEE sample of a surviving path (radiance of the sampled direction, :262-280);
+            // the two exclude each other per lane.  directionToUV (atan2f + acosf) and the bilinear fetch are the longest
+            // straight-line code of this kernel and were 27 % of its instructions when each case evaluated them on its own
+            // (2 and 14 of 32 lanes per instruction, profiles/r1j_shade_full.md): both kinds of lanes now go through ONE
+            // evaluation.  Per lane the order of RNG draws and of the additions into Ei is unchanged.
+            bool envBg = false, envPdf = false, neeEnv = false;
+            f3 envDir = rayDir;
+            float neePdfW = 0.0f;
+            if (escaped && params.useEnvMap)
             {
-                float weight = 1.0f;
-                f3 bg = mk3(0.0f);
-                if (params.useEnvMap)
-                {
-                    const bool wantBg = len == 1u || params.sampleImpl;
-                    const bool wantPdf = params.sampleImpl && params.sampleExpl && len > 1u && !lastSpecular;
-                    float u = 0.0f, v = 0.0f;
-                    if (wantBg || wantPdf) directionToUV(rayDir, u, v); // one atan2f + acosf for both look-ups
-                    if (wantBg) bg = envLinear(env, u, v) * params.envMapStrength;
-                    if (wantPdf)
-                    {
-                        const float lightPickProb = lastPickProb;
-                        const float directPdfW = envMapPdfUV(env, rayDir, u, v);
-                        weight = (lastPdfW * lightPickProb) / (lastPdfW * lightPickProb + directPdfW);
-                    }
-                }
-                Ei = Ei + weight * T * bg;
-                terminate = true;
-            }
-            else if (params.useAreaLight && areaLightHit && !terminate) // implicit area-light hit (:126-146)
-            {
-                float misWeight = 1.0f;
-                if (params.sampleExpl && len > 1u && !lastSpecular)
-                {
-                    const float directPdfA = recip(4.0f * params.areaLight.size.x * params.areaLight.size.y);
-                    const float directPdfW = pdfAtoW(directPdfA, length(hitP - rayOrig), -dot(rayDir, hitN));
-                    const float lightPickProb = lastPickProb;
-                    misWeight = lastPdfW / (lastPdfW + directPdfW * lightPickProb);
-                }
-                Ei = Ei + T * misWeight * ld3(params.areaLight.E);
-                terminate = true;
+                envBg = len == 1u || params.sampleImpl;
+                envPdf = params.sampleImpl && params.sampleExpl && len > 1u && !lastSpecular;
             }
 
-            if (shadowBlocked == 0u) Ei = Ei + neeContrib; // resolved after the implicit terms, as the reference orders it
-
-            if (terminate) // splat and hand the slot back to raygen (:171-205)
-            {
-                bool admit;
-                if (checkSpp)
-                {
-                    admit = false;
-                    if (!maxSamplesReached) admit = (atomicAdd(&fb.spp[pixIdx], 1u) <= params.maxSpp) && len > 0u; // `<=`: quirk kept
-                    if (fb.spp[pixIdx] > params.maxSpp) fb.spp[pixIdx] = params.maxSpp;
-                    splatted = admit;
-                }
-                else admit = len > 0u;
-                if (admit) atomicAdd(&fb.pixels[pixIdx], make_float4(Ei.x, Ei.y, Ei.z, 1.0f));
-            }
-            else
+            if (survives)
             {
                 // surviving path: shading normal, backface flip (:208-241)
                 const flx_material *mp = md.materials + matId;
@@ -211,12 +180,11 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
                             sampleEnvMapAlias(rnd(seed), L, directPdfW, env);
                             const float lenL = params.worldRadius + params.worldRadius;
                             const float cosTh = fmaxf(0.0f, dot(L, hitN));
-                            const f3 envMapLi = evalEnvMapDir(env, L) * params.envMapStrength;
                             st.shw0[gid] = mk4(orig, lenL);
                             st.shw1[gid] = mk4(L, cosTh);
-                            st.nee0[gid] = mk4(envMapLi, directPdfW);
                             st.lastPickProb[gid] = envMapProb;
                             pushShadow = true;
+                            neeEnv = true; envDir = L; neePdfW = directPdfW; // radiance of L: shared evaluation below
                         }
                         if (useArea)
                         {
@@ -242,6 +210,56 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
                     }
                 }
                 matQ = materialQueueOf(mtype, separate);
+            }
+
+            f3 envLi = mk3(0.0f);
+            float envWeight = 1.0f;
+            if (envBg || envPdf || neeEnv) // the shared environment evaluation
+            {
+                float u, v;
+                directionToUV(envDir, u, v);
+                if (envBg || neeEnv) envLi = envLinear(env, u, v) * params.envMapStrength;
+                if (envPdf)
+                {
+                    const float lightPickProb = lastPickProb;
+                    const float directPdfW = envMapPdfUV(env, rayDir, u, v);
+                    envWeight = (lastPdfW * lightPickProb) / (lastPdfW * lightPickProb + directPdfW);
+                }
+                if (neeEnv) st.nee0[gid] = mk4(envLi, neePdfW);
+            }
+            if (escaped) // implicit environment sample with MIS (:99-122)
+            {
+                Ei = Ei + envWeight * T * envLi;
+                terminate = true;
+            }
+            else if (lightHit) // implicit area-light hit (:126-146)
+            {
+                float misWeight = 1.0f;
+                if (params.sampleExpl && len > 1u && !lastSpecular)
+                {
+                    const float directPdfA = recip(4.0f * params.areaLight.size.x * params.areaLight.size.y);
+                    const float directPdfW = pdfAtoW(directPdfA, length(hitP - rayOrig), -dot(rayDir, hitN));
+                    const float lightPickProb = lastPickProb;
+                    misWeight = lastPdfW / (lastPdfW + directPdfW * lightPickProb);
+                }
+                Ei = Ei + T * misWeight * ld3(params.areaLight.E);
+                terminate = true;
+            }
+
+            if (shadowBlocked == 0u) Ei = Ei + neeContrib; // resolved after the implicit terms, as the reference orders it
+
+            if (terminate) // splat and hand the slot back to raygen (:171-205)
+            {
+                bool admit;
+                if (checkSpp)
+                {
+                    admit = false;
+                    if (!maxSamplesReached) admit = (atomicAdd(&fb.spp[pixIdx], 1u) <= params.maxSpp) && len > 0u; // `<=`: quirk kept
+                    if (fb.spp[pixIdx] > params.maxSpp) fb.spp[pixIdx] = params.maxSpp;
+                    splatted = admit;
+                }
+                else admit = len > 0u;
+                if (admit) atomicAdd(&fb.pixels[pixIdx], make_float4(Ei.x, Ei.y, Ei.z, 1.0f));
             }
             if (!(REGEN && terminate)) // a regenerated path overwrites both below
             {
