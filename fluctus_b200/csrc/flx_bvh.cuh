@@ -31,10 +31,10 @@ struct DevBVH
 };
 
 // Top of the tree in shared memory: FLX_TOP_NODES x 64 B per CTA, stored as four float4 planes (plane k holds
-// float4 k of every node) so that lanes reading different nodes spread over the banks.  880 nodes = 56 320 B,
-// one CTA of 1024 threads per SM (see flx_trace.cu).
+// float4 k of every node) so that lanes reading different nodes spread over the banks.  440 nodes = 28 160 B per CTA,
+// two CTAs of 640 threads per SM (see flx_trace.cu).
 #ifndef FLX_TOP_NODES
-#define FLX_TOP_NODES 880
+#define FLX_TOP_NODES 440
 #endif
 #define FLX_TOP_SMEM_BYTES (FLX_TOP_NODES * 64)
 

@@ -7,11 +7,17 @@
 // triangle tests, hits, rays) for the algorithmic-bytes figure; they are never the timed ones.
 #include "flx_internal.h"
 
+// Two CTAs of 640 threads per SM (40 warps at 48 registers) instead of one of 1024 (32 warps at 64): traversal time
+// follows the number of resident warps (768 / 896 / 1024 threads: 126 / 115 / 108 ms per kitchen frame), and 1280
+// threads x 48 registers is the largest population whose loop bodies stay (almost) free of spills — 2 x 672 and
+// 2 x 704 drop to 40 registers and spill 200 bytes.  Each CTA stages its own copy of the top of the tree, so the
+// copy is halved to 440 nodes (flx_bvh.cuh), the plateau of that parameter.  cfg5: 2 731 -> 2 965 Mrays/s, kitchen
+// traversal 108.3 -> 106.8 ms per frame (tools/tune_trace.sh).
 #ifndef FLX_TRACE_THREADS
-#define FLX_TRACE_THREADS 1024
+#define FLX_TRACE_THREADS 640
 #endif
 #ifndef FLX_TRACE_MIN_BLOCKS
-#define FLX_TRACE_MIN_BLOCKS 1
+#define FLX_TRACE_MIN_BLOCKS 2
 #endif
 
 template <bool BITS> struct TrailOf { typedef StackTrail type; };
@@ -375,9 +381,9 @@ k_any_batch(DevBVH bvh, const float4 *__restrict__ rays, unsigned int n, unsigne
 }
 
 // ---------------------------------------------------------------------------------------------
-// One persistent CTA of 1024 threads per SM: a single 55 KB copy of the top of the tree per SM.  Smaller CTAs
-// need one copy each, and the shared-memory carve-out then eats the L1 the deeper nodes and the triangles live
-// in (8 x 28 KB copies cost 8 % on the kitchen render and 17 % on incoherent rays; tools/tune_vote.sh).
+// Persistent grid: FLX_TRACE_MIN_BLOCKS CTAs per SM, each with its own copy of the top of the tree (see the top of this
+// file).  Many small CTAs do not pay: eight 28 KB copies evict the L1 that the deeper nodes and the triangles live in
+// (-8 % on the kitchen render, -17 % on incoherent rays; tools/tune_vote.sh).
 #ifndef FLX_TRACE_CTAS_PER_SM
 #define FLX_TRACE_CTAS_PER_SM ((1024 / FLX_TRACE_THREADS) > FLX_TRACE_MIN_BLOCKS ? (1024 / FLX_TRACE_THREADS) : FLX_TRACE_MIN_BLOCKS)
 #endif
