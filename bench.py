@@ -467,7 +467,7 @@ def run_ours(args):
                          "algorithmic_gb_per_launch": (ext_bytes + shw_bytes) / max(ext_n, 1) / 1e9,
                          "note": "the tree of this scene (37 MB) is served from L1/L2: DRAM traffic is a fraction of the algorithmic "
                                  "bytes (so achieved can exceed the HBM peak) and the kernel is bound by instruction issue, not by HBM "
-                                 "(profiles/r1i_k_ext_shadow_full.md)",
+                                 "(profiles/r1l_k_ext_shadow_full.md)",
                          "launches": int(ext_n), "avg_launch_ms": ext_ms / max(ext_n, 1),
                          "algorithmic_bytes_per_ray": {"extension": ext_per_ray, "shadow": shw_per_ray},
                          "rays_per_launch": {"extension": r["local"]["extension"] / max(ext_n, 1), "shadow": r["local"]["shadow"] / max(ext_n, 1)},

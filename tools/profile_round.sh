@@ -1,5 +1,5 @@
 #!/bin/bash
-# The evidence run kept under profiles/ (run on the GPU box: gpurun -- 'bash tools/profile_round.sh r1f'):
+# The evidence run kept under profiles/ (run on the GPU box: gpurun -- 'bash tools/profile_round.sh r1l'):
 #   1. the full default bench line (never under a profiler),
 #   2. the ncu launch list of a short bench command (gpu__time_duration.sum only: shares, not absolutes),
 #   3. one `ncu --set full` capture of the traversal launch at a steady-state iteration.
