@@ -76,17 +76,27 @@ int flx_create(flx_ctx **out, int device, uint32_t num_tasks, void *cuda_stream)
     // path state: twelve float4 streams + five scalar streams, zero-initialised like a fresh cl::Buffer
     // is not — the oracle starts from zeros too, so untouched fields compare equal.
     const size_t N = num_tasks;
-    const size_t stateBytes = N * (FLX_STATE_VEC_STREAMS * sizeof(float4) + FLX_STATE_SCALAR_STREAMS * 4);
+    const size_t stateBytes = FLX_STATE_AOS ? N * (size_t)FLX_STATE_RECORD_BYTES
+                                            : N * (FLX_STATE_VEC_STREAMS * sizeof(float4) + FLX_STATE_SCALAR_STREAMS * 4);
     CREATE_CUDA(cudaMalloc(&ctx->stateBlock, stateBytes));
     CREATE_CUDA(cudaMemsetAsync(ctx->stateBlock, 0, stateBytes, ctx->stream));
     {
-        float4 *v = (float4 *)ctx->stateBlock;
-        float4 **dst[FLX_STATE_VEC_STREAMS] = {&ctx->st.ray0, &ctx->st.ray1, &ctx->st.hit0, &ctx->st.hit1, &ctx->st.hit2, &ctx->st.thr,
-                                               &ctx->st.acc, &ctx->st.shw0, &ctx->st.shw1, &ctx->st.nee0, &ctx->st.nee1, &ctx->st.nee2};
-        for (int i = 0; i < FLX_STATE_VEC_STREAMS; i++) *dst[i] = v + (size_t)i * N;
-        uint32_t *s = (uint32_t *)(v + (size_t)FLX_STATE_VEC_STREAMS * N);
-        ctx->st.lastSpecular = s; ctx->st.shadowBlocked = s + N; ctx->st.logicFlags = s + 2 * N; ctx->st.lastPickProb = (float *)(s + 3 * N);
-        ctx->st.phase = (int32_t *)(s + 4 * N);
+        char *b = (char *)ctx->stateBlock;
+        PathState &st = ctx->st;
+        StateView<float4> *vec[FLX_STATE_VEC_STREAMS] = {&st.ray0, &st.ray1, &st.thr, &st.acc, &st.hit0, &st.hit1, &st.hit2, &st.shw0,
+                                                         &st.shw1, &st.nee0, &st.nee1, &st.nee2};
+#if FLX_STATE_AOS
+        // byte offsets inside the 256-byte record: four 64-byte groups, fields that are gathered together share one
+        const int vecOff[FLX_STATE_VEC_STREAMS] = {0, 16, 32, 48, 64, 80, 96, 128, 144, 160, 176, 192};
+        for (int i = 0; i < FLX_STATE_VEC_STREAMS; i++) vec[i]->base = b + vecOff[i];
+        st.lastSpecular.base = b + 112; st.shadowBlocked.base = b + 116; st.logicFlags.base = b + 120; st.lastPickProb.base = b + 124;
+        st.phase.base = b + 208;
+#else
+        for (int i = 0; i < FLX_STATE_VEC_STREAMS; i++) vec[i]->base = b + (size_t)i * N * sizeof(float4);
+        char *s = b + (size_t)FLX_STATE_VEC_STREAMS * N * sizeof(float4);
+        st.lastSpecular.base = s; st.shadowBlocked.base = s + 4 * N; st.logicFlags.base = s + 8 * N; st.lastPickProb.base = s + 12 * N;
+        st.phase.base = s + 16 * N;
+#endif
     }
     // queues + counters + cursors + totals
     const size_t queueBytes = FLX_NUM_QUEUES * N * 4 + 512;

@@ -27,12 +27,30 @@
 //   nee2  lastT.xyz      | (spare)           written by material
 //   scalars: lastSpecular (material), shadowBlocked (shadow, logic), logicFlags = backface |
 //            firstDiffuse<<1 (logic), lastPickProb (logic)
+// Every field is reached as st.field[gid] through a strided view, so the layout is a build-time choice:
+//   FLX_STATE_AOS = 0 (default): one stream per field (stride = sizeof(field)), coalesced for the dense stages;
+//   FLX_STATE_AOS = 1 (experiment): one 256-byte record per path — {ray0 ray1 thr acc | hit0 hit1 hit2
+//   scalars | shw0 shw1 nee0 nee1 | nee2 phase} — meant to let the stages that GATHER by sparse path id (material queues,
+//   ray queues) use whole DRAM atoms; measured slower in every stage (logic +41 %, materials +14 %, traversal +3 %).
+#ifndef FLX_STATE_AOS
+#define FLX_STATE_AOS 0
+#endif
+#define FLX_STATE_RECORD_BYTES 256
+template <class T>
+struct StateView
+{
+    char *base;
+    __host__ __device__ __forceinline__ T &operator[](size_t i) const
+    {
+        return *(T *)(base + i * (size_t)(FLX_STATE_AOS ? FLX_STATE_RECORD_BYTES : sizeof(T)));
+    }
+};
 struct PathState
 {
-    float4 *ray0, *ray1, *hit0, *hit1, *hit2, *thr, *acc, *shw0, *shw1, *nee0, *nee1, *nee2;
-    uint32_t *lastSpecular, *shadowBlocked, *logicFlags;
-    float *lastPickProb;
-    int32_t *phase; // microkernel renderer only (PathPhase, geom.h:205-216)
+    StateView<float4> ray0, ray1, hit0, hit1, hit2, thr, acc, shw0, shw1, nee0, nee1, nee2;
+    StateView<uint32_t> lastSpecular, shadowBlocked, logicFlags;
+    StateView<float> lastPickProb;
+    StateView<int32_t> phase; // microkernel renderer only (PathPhase, geom.h:205-216)
 };
 // PathPhase (geom.h:205-216) and the values the microkernel stages park in shadowBlocked while a shadow ray is out
 enum { FLX_MK_RT_NEXT_VERTEX = 0, FLX_MK_SAMPLE_BSDF = 1, FLX_MK_SPLAT_SAMPLE = 4, FLX_MK_GENERATE_CAMERA_RAY = 5, FLX_MK_DONE = 6 };
