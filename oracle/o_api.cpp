@@ -114,6 +114,7 @@ void orc_wf_set_options(void *h, int useBitstack, int denoiserAOV, uint32_t seed
 {
     Wavefront *w = (Wavefront *)h; w->useBitstack = useBitstack != 0; w->denoiserAOV = denoiserAOV != 0; w->seedOffset = seedOffset;
 }
+void orc_wf_set_drop_mixed(void *h, int drop) { ((Wavefront *)h)->dropMixed = drop != 0; }
 
 void orc_wf_reset(void *h) { ((Wavefront *)h)->reset(); }
 void orc_wf_raygen(void *h) { ((Wavefront *)h)->raygen(); }

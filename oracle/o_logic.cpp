@@ -11,16 +11,17 @@ static inline void atomicAddF(float *p, float v)
 }
 
 // wf_logic.cl:352-407 (addToMaterialQueueNaive) incl. -DWF_SINGLE_MAT_QUEUE.  BXDF_MIXED falls
-// into `default:` in the reference and the path is dropped; the oracle routes it
-// to the diffuse queue like the single-queue mode does — documented deviation shared with the
-// CUDA path.
+// into `default:` in the reference and the path is dropped: reproduced when
+// `dropMixed` is set (tests/test_reference_source_cpu.py does, to stay bit-identical with the
+// reference's own code); otherwise it goes to the diffuse queue like the single-queue mode does —
+// the documented deviation of the CUDA path.
 static inline void addToMaterialQueue(Wavefront &w, uint32_t gid, int type)
 {
     if (!w.params.wfSeparateQueues) { w.push(FLX_Q_DIFFUSE, &w.cnt.diffuseQueue, gid); return; }
     switch (type)
     {
-    case FLX_BXDF_DIFFUSE:
-    case FLX_BXDF_MIXED: w.push(FLX_Q_DIFFUSE, &w.cnt.diffuseQueue, gid); break;
+    case FLX_BXDF_MIXED: if (w.dropMixed) break; // fall through
+    case FLX_BXDF_DIFFUSE: w.push(FLX_Q_DIFFUSE, &w.cnt.diffuseQueue, gid); break;
     case FLX_BXDF_GLOSSY: w.push(FLX_Q_GLOSSY, &w.cnt.glossyQueue, gid); break;
     case FLX_BXDF_GGX_ROUGH_REFLECTION: w.push(FLX_Q_GGX_REFL, &w.cnt.ggxReflQueue, gid); break;
     case FLX_BXDF_GGX_ROUGH_DIELECTRIC: w.push(FLX_Q_GGX_REFR, &w.cnt.ggxRefrQueue, gid); break;

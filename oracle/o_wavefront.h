@@ -14,6 +14,7 @@ struct Wavefront
     ShadeScene shade;
     bool useBitstack = false;       // -DUSE_BITSTACK
     bool denoiserAOV = false;       // -DUSE_OPTIX_DENOISER (AOV accumulation only)
+    bool dropMixed = false;         // reference-exact handling of BXDF_MIXED with separate queues (wf_logic.cl:399-401)
     uint32_t seedOffset = 0;        // rank * N for multi-GPU decorrelation; 0 = reference
     uint32_t currPixelIdx = 0;      // deviceBuffers.currentPixelIdx
     flx_queue_counters cnt;         // deviceBuffers.queueCounters

@@ -146,6 +146,10 @@ class OracleWavefront:
     def set_options(self, bitstack=False, denoiser_aov=False, seed_offset=0):
         self.L.orc_wf_set_options(self.h, C.c_int(int(bitstack)), C.c_int(int(denoiser_aov)), U32(seed_offset))
 
+    def set_drop_mixed(self, drop=True):
+        """Reference-exact BXDF_MIXED with separate queues: the path is dropped (wf_logic.cl:399-401)."""
+        self.L.orc_wf_set_drop_mixed(self.h, C.c_int(int(drop)))
+
     # stages
     def reset(self): self.L.orc_wf_reset(self.h)
     def raygen(self): self.L.orc_wf_raygen(self.h)
