@@ -20,9 +20,10 @@ grows (each rank traces its own N paths with rank-offset seeds): weak scaling.
           the tonemapped frame + counters read back to pinned host memory inside the timed region
   roofline : the traversal launch (k_ext_shadow: extension closest-hit + shadow any-hit rays of an iteration),
           algorithmic bytes of SURVEY.md §8(d) / DESIGN.md
-  cpu_baseline / --impl reference : the CPU restatement of the reference's OpenCL kernels
-          (oracle/, OpenMP over work-items) on the host cores — the reference's own device code
-          needs an OpenCL runtime that does not exist on this box.
+  cpu_baseline / --impl reference : the reference's own OpenCL kernels compiled as C++ (oracle/_ref, see
+          oracle/refcl.py), OpenMP over work-items, on the host cores
+  reference_opencl : the reference's untouched kernels on the SAME B200 through NVIDIA's OpenCL platform
+          (oracle/clrun.py): the benchmark frame and the cfg5 ray batch, beside our numbers
 """
 import argparse
 import json
@@ -141,16 +142,23 @@ def measured_peak_gbs():
 
 
 # ---------------------------------------------------------------------------------------------------
-# CPU arm: the oracle's restatement of the reference's .cl kernels, OpenMP over work-items
+# CPU arm: the reference's own kernels (src/*.cl compiled as C++ into oracle/_ref, oracle/refcl.py), work-items spread
+# over the host cores with OpenMP; the oracle port stands in only where those objects were never built.
 class CpuWavefront:
     def __init__(self, scene, env, settings):
-        from oracle import pyoracle  # allowed here: cpu_baseline / --impl reference legs only
+        from oracle import pyoracle, refcl  # allowed here: cpu_baseline / --impl reference legs only
         from fluctus_b200 import abi, scene as fs
-        self.po = pyoracle
         # all the host cores this process may use (torchrun exports OMP_NUM_THREADS=1, which is not the machine)
         self.threads = max(pyoracle.max_threads(), len(os.sched_getaffinity(0)))
-        pyoracle.set_threads(self.threads)
-        self.wf = pyoracle.OracleWavefront(CPU_TASKS, WIDTH, HEIGHT)
+        try:
+            refcl.program("wf_logic", refcl.Options(use_area_light=True, use_env_map=True, separate_queues=settings.get("separate_queues", True)))
+            self.kind = "reference"
+            self.wf = refcl.RefWavefront(CPU_TASKS, WIDTH, HEIGHT)
+            self.wf.set_threads(self.threads)
+        except RuntimeError:
+            self.kind = "port"
+            pyoracle.set_threads(self.threads)
+            self.wf = pyoracle.OracleWavefront(CPU_TASKS, WIDTH, HEIGHT)
         self.wf.set_scene(scene)
         self.wf.set_envmap(env)
         p = abi.make_render_params(WIDTH, HEIGHT, n_tris=len(scene["tris"]), world_radius=fs.world_radius(scene), **settings)
@@ -185,15 +193,16 @@ def cpu_baseline(scene, env, settings, budget_s=12.0):
         dt = time.perf_counter() - t0
         if dt >= budget_s or iters >= 64:
             break
-    return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": cw.threads, "kind": "port",
+    return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": cw.threads, "kind": cw.kind,
             "mrays_per_s": rays / dt / 1e6,
             "sample": "%d steady-state wavefront iterations of a %d-path pool (after %d untimed ramp-up iterations), "
                       "same scene / resolution / params; %.1f s" % (iters, CPU_TASKS, CPU_RAMP_ITERS, dt)}
 
 
 def run_reference_arm(args):
-    """--impl reference: the reference's algorithm on the host cores (oracle port; the OpenCL device
-    code itself has no runtime here).  Rank 0 only."""
+    """--impl reference: the reference's own kernels on the host cores (oracle/_ref: src/*.cl compiled as C++; the
+    timing of the same kernels on the B200 through NVIDIA's OpenCL platform is the `reference_opencl` block of
+    the other arm's line).  Rank 0 only."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     teapot, scene, env, settings = load_workload()
@@ -214,9 +223,58 @@ def run_reference_arm(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": config_dict(args.gpus, scene, "reference"),
-        "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": cw.threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": cw.threads, "kind": cw.kind, "sample": sample},
         "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0})
+
+
+def reference_opencl(scene, env, settings, ours_hit_i=None, rays=None, grid=None):
+    """The reference's untouched kernels on this GPU through its OpenCL platform (oracle/clrun.py), after the timed
+    regions: (1) the benchmark frame — reset + ITERS_PER_STEP iterations + tonemap + frame read-back, host loop as in
+    Tracer::runBenchmarkFromFile (one blocking counter read per iteration) — with the benchmark's pool and queues and
+    with the reference's defaults (wfBufferSize 2^20, single material queue); (2) the cfg5 ray batch through
+    traceExtension, compared ray by ray with our result.  None where the box has no OpenCL device."""
+    try:
+        from oracle import clrun
+        ok, what = clrun.available()
+        if not ok:
+            return {"unavailable": what}
+        from fluctus_b200 import abi, scene as fs
+        out = {"device": what, "build_options": " ".join(o for o in clrun.global_build_options("reference") if not o.startswith("/")).replace("-I ", "-I<reference>/src "),
+               "frames": {}}
+        for tag, n_tasks, sepq in (("benchmark settings (2^%d paths, separate queues)" % int(np.log2(NUM_TASKS)), NUM_TASKS, True),
+                                   ("reference defaults (2^20 paths, single material queue)", 1 << 20, False)):
+            st = dict(settings); st["separate_queues"] = sepq
+            p = abi.make_render_params(WIDTH, HEIGHT, n_tris=len(scene["tris"]), world_radius=fs.world_radius(scene), **st)
+            cl = clrun.CLWavefront(n_tasks, WIDTH, HEIGHT, "reference")
+            cl.set_scene(scene); cl.set_envmap(env); cl.set_params(p.tobytes())
+            cl.render(4)
+            best = None
+            for _ in range(3):
+                t0 = time.perf_counter()
+                it, tot = cl.render(ITERS_PER_STEP)
+                cl.postprocess()
+                dt = time.perf_counter() - t0
+                if best is None or dt < best[0]:
+                    best = (dt, tot)
+            cl.timing = True; cl.kernel_ms.clear()
+            cl.render(ITERS_PER_STEP)
+            km = {k: round(v[0], 2) for k, v in cl.kernel_ms.items()}
+            cl.close()
+            out["frames"][tag] = {"msamples_per_s": best[1]["samples"] / best[0] / 1e6, "frame_ms": best[0] * 1e3,
+                                  "mrays_per_s": (best[1]["extension"] + best[1]["shadow"]) / best[0] / 1e6,
+                                  "kernel_ms_per_frame": km, "kernel_ms_sum": round(sum(km.values()), 1)}
+        if rays is not None:
+            r = clrun.trace_closest(grid, rays, mode="reference")
+            d = r["hit_i"] != ours_hit_i
+            out["raycast"] = {"mrays_per_s": len(rays) / r["ms"] / 1e3, "kernel_ms": r["ms"], "rays": int(len(rays)),
+                              "hit_miss_differs_from_ours": int(((r["hit_i"] >= 0) != (ours_hit_i >= 0)).sum()),
+                              "hit_index_differs_from_ours": int(d.sum()),
+                              "note": "the reference's bits are device-defined (fast-relaxed-math, FMA contraction, rcp.approx): "
+                                      "tests/test_opencl_reference_gpu.py re-traces every differing ray with the IEEE build of the reference source"}
+        return out
+    except Exception as e:  # never let the bonus block cost the bench line
+        return {"error": str(e)[-400:]}
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -323,15 +381,27 @@ def run_raycast(dev, rank, world, teapot, peak_gbs, steps, warmup, check):
                                     "traffic_source": t["source"]})
     except (OSError, ValueError, KeyError):
         pass
-    if check and rank == 0:  # spot parity against the oracle (checker only; tests/ hold the full comparison)
-        from oracle import pyoracle
-        m = 1 << 15
+    keep = None
+    if check and rank == 0:  # parity sample against the oracle (checker only; tests/ hold the full 2^24 comparison) + CPU rate
+        from oracle import pyoracle, refcl
+        m = 1 << 20
+        threads = max(pyoracle.max_threads(), len(os.sched_getaffinity(0)))
+        pyoracle.set_threads(threads)
         ref = pyoracle.trace_closest(grid, rays[:m], 0)
-        gi, gt = d_i[:m].cpu().numpy(), d_t[:m].cpu().numpy()
-        res["parity"] = {"rays_checked": m, "hit_i_equal": bool(np.array_equal(gi, ref["hit_i"])),
-                         "hit_t_bits_equal": bool(np.array_equal(gt.view(np.uint32), ref["hit_t"].view(np.uint32)))}
+        gi, gt = d_i.cpu().numpy(), d_t.cpu().numpy()
+        res["parity"] = {"rays_checked": m, "hit_i_equal": bool(np.array_equal(gi[:m], ref["hit_i"])),
+                         "hit_t_bits_equal": bool(np.array_equal(gt[:m].view(np.uint32), ref["hit_t"].view(np.uint32)))}
+        try:  # the reference's bvh_intersect on all host cores, beside the GPU figure
+            t0 = time.perf_counter()
+            refcl.trace_closest(grid, rays[:m], threads=threads)
+            dt = time.perf_counter() - t0
+            res["cpu_baseline"] = {"value": m / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "reference",
+                                   "sample": "the first 2^20 rays of the batch through the reference's bvh_intersect (src/bvh.cl compiled as C++), %.1f s" % dt}
+        except RuntimeError as e:
+            res["cpu_baseline"] = {"unavailable": str(e)[:200]}
+        keep = (grid, rays, gi)
     ctx.close()
-    return res
+    return res, keep
 
 
 def run_ours(args):
@@ -444,10 +514,19 @@ def run_ours(args):
 
     raycast = None
     if not args.no_raycast:
-        raycast = run_raycast(dev, rank, world, teapot, peak, max(args.steps // 2, 3), args.warmup, check=(world == 1))
-    cpu = None
+        raycast, keep = run_raycast(dev, rank, world, teapot, peak, max(args.steps // 2, 3), args.warmup, check=(world == 1))
+    else:
+        keep = None
+    cpu = ref_cl = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline(scene, env, settings)
+    if rank == 0 and world == 1 and not args.no_reference_opencl:
+        tr.close()  # free our pools first: the reference's 2^22-path state is another 1.1 GB + the cfg5 tree in its own layout
+        tr = None
+        if keep is not None:
+            ref_cl = reference_opencl(scene, env, settings, ours_hit_i=keep[2], rays=keep[1], grid=keep[0])
+        else:
+            ref_cl = reference_opencl(scene, env, settings)
 
     if rank == 0:
         line = {
@@ -476,10 +555,11 @@ def run_ours(args):
                                      "CUDA events around every stage launch on the context's stream"},
             "stage_ms_per_step": {k: t / args.steps for k, t in stage_ms.items()},
             "events_pass_ms_per_step": r["ms"] / args.steps,
-            "clocks": clk, "cpu_baseline": cpu, "raycast": raycast,
+            "clocks": clk, "cpu_baseline": cpu, "raycast": raycast, "reference_opencl": ref_cl,
         }
         emit(line)
-    tr.close()
+    if tr is not None:
+        tr.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -503,6 +583,7 @@ def main():
     ap.add_argument("--impl", choices=("ours", "reference"), default="ours")
     ap.add_argument("--no-raycast", action="store_true", help="skip the cfg5 ray-cast microbench")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-reference-opencl", action="store_true", help="skip timing the reference's kernels through OpenCL")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON result: libraries that write to fd 1 on their own (NCCL prints its
     # version banner there when NCCL_DEBUG is set) are sent to stderr for the duration of the run.
