@@ -8,7 +8,7 @@ import sys
 
 rep, kid = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", "--kernel-id", ":::" + kid],
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass", ] + (["--kernel-id", ":::" + kid] if kid != "0" else []),
                      capture_output=True, text=True).stdout
 rows, fname, hdr, total = [], "", None, 0
 for r in csv.reader(out.splitlines()):
