@@ -57,6 +57,7 @@ SIGNATURES = {
     "flx_trace_closest": (I32, [V, V, SZ, V, V, V]),
     "flx_trace_any": (I32, [V, V, SZ, V]),
     "flx_trace_closest_device": (I32, [V, V, SZ, V, V, V]),
+    "flx_trace_closest_static": (I32, [V, V, SZ, V, V]),
     "flx_trace_any_device": (I32, [V, V, SZ, V]),
     "flx_export_state": (I32, [V, V]),
     "flx_import_state": (I32, [V, V]),

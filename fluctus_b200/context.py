@@ -182,6 +182,15 @@ class CudaContext:
         self._check(self.L.flx_trace_closest(self.h, _p(rays), n, _p(hit_i), _p(hit_t), _p(hits)))
         return (hit_i, hit_t, hits) if want_hits else (hit_i, hit_t)
 
+    def traceClosestStatic(self, rays):
+        """flx_trace_closest_static: no allocation on the call path (staging in a static device array, at most
+        FLX_STATIC_MAX_RAYS = 262144 rays per call).  No reference counterpart."""
+        rays = np.ascontiguousarray(rays, np.float32)
+        n = rays.shape[0]
+        hit_i, hit_t = np.empty(n, np.int32), np.empty(n, np.float32)
+        self._check(self.L.flx_trace_closest_static(self.h, _p(rays), n, _p(hit_i), _p(hit_t)))
+        return hit_i, hit_t
+
     def traceAny(self, rays):
         rays = np.ascontiguousarray(rays, np.float32)
         occ = np.empty(rays.shape[0], np.uint8)

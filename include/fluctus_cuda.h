@@ -169,6 +169,20 @@ int flx_trace_any(flx_ctx *ctx, const float *rays, size_t n, uint8_t *occluded);
 int flx_trace_closest_device(flx_ctx *ctx, const void *d_rays, size_t n, void *d_hit_i, void *d_hit_t, void *d_hits);
 int flx_trace_any_device(flx_ctx *ctx, const void *d_rays, size_t n, void *d_occluded);
 
+/* ---- ray cast without allocation (NO counterpart in the reference) ----
+ * flx_trace_closest for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it): same arguments minus the hit records, same results bit for bit, but the device staging
+ * of rays and results lives in a file-scope static device array instead of a scratch block that grows with
+ * cudaMalloc.  The call path contains no cudaMalloc / cudaFree / allocating library routine.  Limits and rules:
+ *   - at most FLX_STATIC_MAX_RAYS rays per call; a larger n is rejected with FLX_ERR_ARG and a message;
+ *   - every GPU that loads the library holds the array (10.0 MiB) until the process exits;
+ *   - the array is shared by ALL contexts on a device and keeps the last call's contents (the call clears what must
+ *     start at zero); calls that overlap on the GPU race on it — serialise them.  The call synchronises the
+ *     context's stream before it returns.
+ * rays: n x 8 floats as for flx_trace_closest (host memory); hit_i / hit_t: n entries each (host memory), required. */
+#define FLX_STATIC_MAX_RAYS 262144u
+int flx_trace_closest_static(flx_ctx *ctx, const float *rays, size_t n, int32_t *hit_i, float *hit_t);
+
 /* ---- state inspection for stage-by-stage parity (no reference counterpart; the reference's
  * copyToHost helper, clcontext.cpp:103-115, is the nearest thing) -------------------------------- */
 int flx_export_state(flx_ctx *ctx, uint32_t *slots64xN); /* reference SoA layout, see fluctus_abi.h */
