@@ -3,8 +3,10 @@
 // IEEE-754 binary32, round-to-nearest-even, no FMA contraction (-ffp-contract=off), denormals
 // kept, native_recip(x) = 1.0f/x, rsqrt(x) = 1.0f/sqrtf(x), length = sqrtf(dot),
 // normalize(v) = v * (1.0f/length(v)), dot/cross written out left to right, fmin/fmax
-// NaN-ignoring (C fminf/fmaxf).  Parity status: UNPINNED by the reference (it ships no tests or
-// golden vectors and its OpenCL runtime is absent here) — see DESIGN.md "Oracle".
+// NaN-ignoring (C fminf/fmaxf).  Parity status: PINNED — tests/test_reference_source_cpu.py asserts
+// this restatement bit-identical to the reference's own .cl sources compiled as C++ (oracle/refcl.py), and
+// tests/test_opencl_reference_gpu.py checks the CUDA path against the reference's untouched kernels on the
+// B200's OpenCL platform — see DESIGN.md §4.
 #pragma once
 #include <cmath>
 #include <cstdint>
