@@ -255,6 +255,10 @@ k_logic(PathState st, Queues qs, FrameBuffers fb, MaterialsDev md, EnvMapDev env
                 {
                     admit = false;
                     if (!maxSamplesReached) admit = (atomicAdd(&fb.spp[pixIdx], 1u) <= params.maxSpp) && len > 0u; // `<=`: quirk kept
+                    // The reference clamps the counter with a plain read + write (wf_logic.cl:186-189): a benign race, kept.
+                    // Paths that passed the first check above before the clamp set the counter back to maxSpp are admitted
+                    // again by the `<=`, so a pixel many paths finish on at once can end with maxSpp + 2 (rarely more)
+                    // samples instead of maxSpp + 1; splattedSamples counts every one of them, the image stays unbiased.
                     if (fb.spp[pixIdx] > params.maxSpp) fb.spp[pixIdx] = params.maxSpp;
                     splatted = admit;
                 }

@@ -213,11 +213,18 @@ public:
     {
         const uint64_t target = (uint64_t)spp * params.width * params.height;
         CudaContext::Totals t{};
+        uint64_t lastSplatted = ~0ull;
         for (uint32_t done = 0; done < maxIterations; done += batch)
         {
             clctx.render(std::min(batch, maxIterations - done));
             t = clctx.getRenderTotals();
             if (spp && (params.maxSpp > 0 ? t.splatted : t.samples) >= target) break;
+            // CHECK_SPP budget exhausted: every pixel is saturated, nothing was splatted in a whole batch.  The
+            // reference's stop rule `sampleCount >= w*h*maxSpp` (src/tracer.cpp:713,730,773) can then never be met — its
+            // first logic pass saturates samplesPerPixel[0] without splatting, so the total
+            // tops out at target - maxSpp unless racing paths slip extra samples in — and the loop would spin forever.
+            if (params.maxSpp > 0 && t.splatted == lastSplatted) break;
+            lastSplatted = t.splatted;
         }
         clctx.enqueuePostprocessKernel(params);
         clctx.finishQueue();

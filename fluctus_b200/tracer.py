@@ -100,12 +100,19 @@ class Tracer:
             return c.getRenderTotals()
         target = int(spp) * int(self.params[0]["width"]) * int(self.params[0]["height"])
         key = "splatted" if int(self.params[0]["maxSpp"]) > 0 else "samples"
-        done = 0
+        done, last = 0, None
         while done < max_iterations:
             c.render(batch)
             done += batch
-            if c.getRenderTotals()[key] >= target:
+            t = c.getRenderTotals()
+            if t[key] >= target:
                 break
+            # CHECK_SPP budget exhausted (every pixel saturated, a whole batch without a splat): the reference's stop rule
+            # can then never be met — its first logic pass saturates samplesPerPixel[0] without splatting (DESIGN.md §7,
+            # quirk 13), so the total tops out at target - maxSpp unless racing paths slip extra samples in
+            if key == "splatted" and t[key] == last:
+                break
+            last = t[key]
         return c.getRenderTotals()
 
     # Tracer::renderSingle (tracer.cpp:108-182): final frame with a predefined spp on the microkernel renderer —

@@ -4,7 +4,8 @@
 // rays traced inline.  This is the mode Tracer::renderSingle uses for an exact sample count per pixel
 // (src/tracer.cpp:108-182): with a fixed pixel<->task map there are no cross-task float atomics, so images
 // are deterministic — the strict image-parity check of tests/test_microkernel_gpu.py.
-// Same state layout and scene as the wavefront oracle (o_wavefront.h); parity unpinned, like the rest.
+// Same state layout and scene as the wavefront oracle (o_wavefront.h); pinned bit for bit to the reference's mk_*.cl
+// compiled as C++ (tests/test_reference_source_cpu.py), like the rest.
 #include "o_wavefront.h"
 #include <cstring>
 

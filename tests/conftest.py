@@ -57,3 +57,14 @@ def psor_cube():
 
 def bits(a):
     return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def pytest_terminal_summary(terminalreporter):
+    """Largest out-of-tolerance fractions the stage comparisons saw (the limits in test_stages_gpu.py are set from these)."""
+    import sys
+    mod = sys.modules.get("test_stages_gpu")
+    if mod is not None and mod.OBSERVED["checks"]:
+        o = mod.OBSERVED
+        terminalreporter.write_line("stage parity: %d state comparisons; largest fraction of paths beyond 1e-4 or with a differing "
+                                    "integer field %.5f (limit %.5f); largest fraction between 1e-5 and 1e-4 %.5f (limit %.5f)"
+                                    % (o["checks"], o["flip"], mod.MAX_FLIP_FRACTION, o["amplified"], mod.MAX_AMPLIFIED_FRACTION))

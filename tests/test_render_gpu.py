@@ -59,23 +59,6 @@ def test_converged_image_matches_oracle(oracle, teapot, night_env, cfg):
     tr.close()
 
 
-def test_update_loop_matches_render_entry(teapot, night_env):
-    """Tracer.update (stage-by-stage calls, host-advanced cursor) and flx_render (CUDA graph,
-    device-side bookkeeping) are the same algorithm: sample counts per iteration must match."""
-    from fluctus_b200 import Tracer
-    kw = dict(max_bounces=3, use_env_map=True, use_area_light=False)
-    a = Tracer(64, 48, num_tasks=4096, **kw)
-    a.init(teapot, night_env)
-    for _ in range(40):
-        a.update()
-    pa = a.pixels()
-    assert a.stats["samples"] > 0 and pa[..., 3].sum() > 0
-    # every splatted sample is counted once: pixel weights == terminated paths with len > 0
-    assert abs(float(pa[..., 3].sum()) - a.stats["samples"]) <= 4096 * 3
-    assert not np.isnan(pa).any()
-    a.close()
-
-
 def test_check_spp_budget_full_resolution(teapot, night_env):
     """Size-independent property at the benchmark resolution: with CHECK_SPP every pixel ends with
     maxSpp or maxSpp+1 samples (the reference's `<=` quirk), never more, and the splatted-sample

@@ -22,6 +22,7 @@ MAX_FLIP_FRACTION = 2e-3  # paths allowed to diverge through a flipped compariso
 # Such paths are counted separately: at most 1 % of the paths may sit between 1e-5 and 1e-4.
 AMPLIFIED_TOL = 1e-4
 MAX_AMPLIFIED_FRACTION = 1e-2
+OBSERVED = {"flip": 0.0, "amplified": 0.0, "checks": 0}  # largest fractions seen by _compare_state in this session
 
 
 def _setup(oracle, scene, env, N, W, H, **kw):
@@ -56,7 +57,11 @@ def _push_oracle_to_gpu(wf, ctx):
     ctx.setPixelIndex(wf.get_pixel_index())
 
 
-def _compare_state(gpu64, ref64, fields, what, allow_flips=True):
+def _compare_state(gpu64, ref64, fields, what, allow_flips=True, vector_norm=False):
+    """vector_norm: judge a vector field relative to the vector's largest component instead of component by component —
+    for comparisons that span several stages (tests/test_fused_gpu.py), where an ulp of the direction travels through
+    P = o + t d and a coordinate that happens to be ~0 (a point on the floor plane y = 0) would otherwise be measured
+    against the 1e-3 floor instead of |P|."""
     from fluctus_b200 import abi
     N = ref64.shape[1]
     bad = np.zeros(N, bool)
@@ -70,9 +75,13 @@ def _compare_state(gpu64, ref64, fields, what, allow_flips=True):
             g64, r64 = g.astype(np.float64), r.astype(np.float64)
             both_nan = np.isnan(g64) & np.isnan(r64)
             same_inf = np.isinf(g64) & (g64 == r64)
+            scale = np.maximum(np.abs(r64), 1e-3)
+            if vector_norm and r64.ndim == 2:
+                with np.errstate(invalid="ignore"):
+                    scale = np.maximum(np.nanmax(np.where(np.isfinite(r64), np.abs(r64), 0.0), axis=1, keepdims=True), 1e-3) * np.ones_like(r64)
             with np.errstate(invalid="ignore"):
-                ok = (np.abs(g64 - r64) <= REL_TOL * np.maximum(np.abs(r64), 1e-3)) | both_nan | same_inf
-                ok2 = (np.abs(g64 - r64) <= AMPLIFIED_TOL * np.maximum(np.abs(r64), 1e-3)) | both_nan | same_inf
+                ok = (np.abs(g64 - r64) <= REL_TOL * scale) | both_nan | same_inf
+                ok2 = (np.abs(g64 - r64) <= AMPLIFIED_TOL * scale) | both_nan | same_inf
             b = ~ok2 if ok2.ndim == 1 else ~ok2.all(1)
             if allow_flips:
                 amplified |= (~ok if ok.ndim == 1 else ~ok.all(1)) & ~b
@@ -83,6 +92,10 @@ def _compare_state(gpu64, ref64, fields, what, allow_flips=True):
             per_field[name] = (int(b.sum()), k, g[k].tolist(), r[k].tolist())
         bad |= b
     frac = bad.mean()
+    if allow_flips:  # observed fractions: printed per test run (pytest -s / -rP) and summarised by conftest at session end
+        OBSERVED["flip"] = max(OBSERVED["flip"], float(frac))
+        OBSERVED["amplified"] = max(OBSERVED["amplified"], float(amplified.mean()))
+        OBSERVED["checks"] += 1
     limit = MAX_FLIP_FRACTION if allow_flips else 0.0
     assert amplified.mean() <= MAX_AMPLIFIED_FRACTION, "%s: %d of %d paths between 1e-5 and 1e-4" % (what, amplified.sum(), N)
     assert frac <= limit, "%s: %d of %d paths differ; per field (count, first gid, gpu, oracle): %s" % (what, bad.sum(), N, per_field)
