@@ -11,8 +11,8 @@ fluctus_b200/standin.py rebuilds a room with the kitchen's material mix from the
 fixture), 1920x1080, 8 bounces, environment-map MIS + area light, NUM_TASKS = 2^22 paths per GPU.
 
 One STEP = one frame: reset, ITERS wavefront iterations (logic+raygen -> materials -> ext+shadow+
-bookkeeping: the reference's benchmark inner loop, src/tracer.cpp:737-778, in three launches), one
-all-reduce of the float accumulation buffer over the ranks, tonemap.  Per-GPU work is fixed as N
+bookkeeping: the reference's benchmark inner loop, src/tracer.cpp:737-778, in three launches), one NCCL
+reduce of the float accumulation buffer into rank 0, tonemap there.  Per-GPU work is fixed as N
 grows (each rank traces its own N paths with rank-offset seeds): weak scaling.
   value : Msamples/s, device-resident, CUDA events around K graph-replayed steps, max over ranks
           (the K steps are then repeated launch by launch with events around every stage: stage times, roofline)
@@ -74,9 +74,9 @@ def config_dict(n_gpus, scene, impl):
                         "env-map MIS + area light" % len(scene["tris"]),
             "num_tasks_per_gpu": NUM_TASKS if impl == "ours" else CPU_TASKS,
             "iterations_per_step": ITERS_PER_STEP if impl == "ours" else CPU_ITERS_PER_STEP,
-            "step": "one frame: reset + iterations + all-reduce + tonemap" if impl == "ours"
+            "step": "one frame: reset + iterations + reduce to rank 0 + tonemap" if impl == "ours"
                     else "steady-state wavefront iterations on the CPU path pool",
-            "parallelism": "sample-sharded x%d, one all-reduce of the accumulation buffer per frame" % n_gpus,
+            "parallelism": "sample-sharded x%d, one NCCL reduce of the accumulation buffer into rank 0 per frame" % n_gpus,
             "l2": "inputs larger than L2: %d MB path state + 33 MB frame per pass (L2 126 MB), no flush needed"
                   % ((NUM_TASKS if impl == "ours" else CPU_TASKS) * 212 // (1 << 20)),
             "stand_in_for": "assets/country_kitchen/Country-Kitchen.obj (stripped from the reference snapshot)"}
@@ -278,18 +278,187 @@ def reference_opencl(scene, env, settings, ours_hit_i=None, rays=None, grid=None
 
 
 # ---------------------------------------------------------------------------------------------------
+# one B200 row per config.  After the timed regions, rank 0, one GPU.
+def _block_relmse(img, ref, W, H, bs):
+    def means(px):
+        px = np.asarray(px, np.float32).reshape(H, W, 4)
+        c = px[..., :3] / np.maximum(px[..., 3:], 1.0)
+        return c[:H // bs * bs, :W // bs * bs].reshape(H // bs, bs, W // bs, bs, 3).mean((1, 3))
+    a, b = means(img), means(ref)
+    return float((((a - b) ** 2) / (b ** 2 + 1e-3)).mean())
+
+
+def config_scenes(teapot):
+    """cfg1 as BASELINE.json states it; cfg2 / cfg3 on stand-ins (luxball.obj and conference.obj are stripped from the
+    reference snapshot) built from the reference's own assets in the scene cache, when it is there."""
+    from fluctus_b200 import abi, scene as fs
+    out = {"cfg1": dict(scene=teapot, W=512, H=512, N=262144, spp=16, oracle_spp=16, bs=4, stand_in_for=None,
+                        what="assets/teapot.ply + env_maps/night.hdr, 512x512, 4 bounces, 16 spp, wfBufferSize 262144 (as stated)",
+                        kw=dict(max_bounces=4, use_env_map=True, use_area_light=False))}
+    cache = os.path.join(ROOT, "scenes", "_cache")
+    try:
+        base = fs.load_scene(os.path.join(cache, "psor_cube_sbvh.npz"))
+        mats = np.tile(base["materials"][:1], 6)
+        types = [abi.BXDF_DIFFUSE, abi.BXDF_GLOSSY, abi.BXDF_GGX_ROUGH_REFLECTION, abi.BXDF_IDEAL_REFLECTION,
+                 abi.BXDF_GGX_ROUGH_DIELECTRIC, abi.BXDF_IDEAL_DIELECTRIC]
+        for k, t in enumerate(types):
+            mats[k]["type"] = t
+            mats[k]["Kd"][:3] = (0.7, 0.45 + 0.05 * k, 0.3); mats[k]["Ks"][:3] = (0.9, 0.85, 0.8)
+            mats[k]["Ns"], mats[k]["Ni"] = 0.12 + 0.04 * k, 1.5
+        tris = base["tris"].copy()
+        tris["matId"] = (np.arange(len(tris)) // 256) % 6
+        scene = dict(base); scene.update(materials=mats, tris=tris)
+        b = base["bounds"]; c = 0.5 * (b[0] + b[1])
+        out["cfg2"] = dict(scene=scene, W=1024, H=1024, N=1 << 20, spp=64, oracle_spp=2, bs=16,
+                           stand_in_for="assets/luxball/luxball.obj (stripped)",
+                           what="psor-cube geometry (18 221 tris) with GGX rough reflection / rough dielectric, ideal dielectric, mirror, "
+                                "glossy and diffuse materials, 1024x1024, 8 bounces, 64 spp, env map + area light",
+                           kw=dict(max_bounces=8, use_env_map=True, use_area_light=True, separate_queues=True,
+                                   cam_pos=(float(c[0]), float(c[1]), float(b[1][2] + 1.2 * (b[1][2] - b[0][2]))),
+                                   light_pos=(float(c[0]) + 2.0, float(b[1][1]) + 1.0, float(c[2]))))
+    except OSError:
+        pass
+    try:
+        from fluctus_b200.standin import conference_standin
+        room, view = conference_standin(fs.load_scene(os.path.join(cache, "egyptcat_sbvh.npz")))
+        out["cfg3"] = dict(scene=room, W=1920, H=1080, N=1 << 22, spp=16, oracle_spp=1, bs=40,
+                           stand_in_for="assets/conference/conference.obj (stripped)",
+                           what="egyptcat.obj instanced 7x1x3 in a closed room (%d tris, textured glossy + diffuse), 1920x1080, 8 bounces, "
+                                "area light only, 16 spp" % len(room["tris"]),
+                           kw=dict(max_bounces=8, use_env_map=False, use_area_light=True, separate_queues=True, **view))
+    except OSError:
+        pass
+    return out
+
+
+def run_configs(dev, stream, teapot, env):
+    """GPU: the config's full sample budget (CHECK_SPP stop rule of Tracer::runBenchmarkFromFile), timed with CUDA events
+    after one warm-up render.  Oracle (checker): the same loop on the host cores with a bounded budget (oracle_spp), block
+    means compared.  relMSE is dominated by the Monte-Carlo noise of the lower-spp side."""
+    import torch
+    import fluctus_b200 as fx
+    from oracle import pyoracle
+    threads = max(pyoracle.max_threads(), len(os.sched_getaffinity(0)))
+    pyoracle.set_threads(threads)
+    res = {}
+    for name, cfg in config_scenes(teapot).items():
+        W, H, N = cfg["W"], cfg["H"], cfg["N"]
+        kw = dict(cfg["kw"], max_spp=cfg["spp"])
+        tr = fx.Tracer(W, H, num_tasks=N, device=dev.index, stream=stream.cuda_stream, **kw)
+        tr.init(cfg["scene"], env if kw.get("use_env_map") else None)
+        tr.render(spp=cfg["spp"])                                     # warm-up (graph capture, caches)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        tot = tr.render(spp=cfg["spp"])
+        tr.clctx.enqueuePostprocessKernel()
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        ms = e0.elapsed_time(e1)
+        img = tr.pixels().reshape(-1, 4).copy()
+        kw_o = dict(cfg["kw"], max_spp=cfg["oracle_spp"])
+        from fluctus_b200 import abi, scene as fs
+        p = abi.make_render_params(W, H, n_tris=len(cfg["scene"]["tris"]), world_radius=fs.world_radius(cfg["scene"]), **kw_o)
+        wf = pyoracle.OracleWavefront(min(N, 1 << 19), W, H)
+        wf.set_scene(cfg["scene"])
+        if kw.get("use_env_map"):
+            wf.set_envmap(env)
+        wf.set_params(p.tobytes())
+        t0, first, iters = time.perf_counter(), True, 0
+        while iters < 4000:
+            it, _ = wf.render(8, first)
+            first = False; iters += it
+            if it < 8 or (wf.spp() >= cfg["oracle_spp"]).all():
+                break
+        t_or = time.perf_counter() - t0
+        ref = wf.pixels().copy()
+        res[name] = {"workload": cfg["what"], "stand_in_for": cfg["stand_in_for"], "triangles": int(len(cfg["scene"]["tris"])),
+                     "msamples_per_s": tot["splatted"] / (ms * 1e-3) / 1e6, "seconds": ms * 1e-3, "samples": int(tot["splatted"]),
+                     "iterations": int(tot["iterations"]), "mrays_per_s": (tot["extension"] + tot["shadow"]) / (ms * 1e-3) / 1e6,
+                     "oracle": {"spp": cfg["oracle_spp"], "seconds": t_or, "cores": threads,
+                                "msamples_per_s": float(ref[:, 3].sum()) / t_or / 1e6},
+                     "relmse_vs_oracle": _block_relmse(img, ref, W, H, cfg["bs"]), "relmse_blocks": "%dx%d pixels" % (cfg["bs"], cfg["bs"])}
+        tr.close()
+    return res
+
+
+def run_headless_cpp(scene, env, settings, n_gpus):
+    """The C++ host (fluctus_headless -> HeadlessTracer -> CudaContext -> the same C-ABI): the benchmark frame rendered by a
+    subprocess of rank 0, sample-sharded over n_gpus devices inside that one process, frames combined by
+    flx_reduce_frames over NVLink peer memory.  Reports the rate the binary prints (render + combine, without scene load)."""
+    import subprocess as sp
+    import tempfile
+    from fluctus_b200 import abi, scene as fs
+    exe = os.path.join(ROOT, "fluctus_b200", "fluctus_headless")
+    if not os.path.exists(exe):
+        return {"unavailable": "fluctus_headless not built"}
+    tmp = tempfile.mkdtemp(prefix="flx_bench_")
+    try:
+        flxs, cfg, state, out = (os.path.join(tmp, n) for n in ("kitchen.flxs", "settings.json", "state.dat", "frame.pfm"))
+        fs.save_flxs(flxs, scene, env)
+        json.dump({"release": {"wfBufferSize": NUM_TASKS, "useAreaLight": True, "useEnvMap": True, "maxPathDepth": MAX_BOUNCES,
+                               "useSeparateQueues": True, "tonemap": 2}}, open(cfg, "w"))
+        p = abi.make_render_params(WIDTH, HEIGHT, n_tris=len(scene["tris"]), world_radius=fs.world_radius(scene), **settings)
+        abi.state_record(p).tofile(state)
+        spp = 12 * n_gpus  # ~ the samples of one bench frame per GPU
+        best = None
+        for _ in range(2):
+            r = sp.run([exe, "-x", str(WIDTH), "-y", str(HEIGHT), "-s", str(spp), "--settings", cfg, "--load-state", state,
+                        "--gpus", str(n_gpus), "--out", out, flxs], capture_output=True, text=True, timeout=300)
+            if r.returncode != 0:
+                return {"error": (r.stderr or r.stdout)[-300:]}
+            st = json.loads(r.stdout.strip().splitlines()[-1])
+            if best is None or st["msamples_per_s"] > best["msamples_per_s"]:
+                best = st
+        return {"msamples_per_s": best["msamples_per_s"], "seconds": best["seconds"], "samples": best["samples"], "gpus": best["gpus"],
+                "spp": spp, "iterations": best["iterations"], "kernel_launches": best["kernel_launches"],
+                "what": "fluctus_headless -x 1920 -y 1080 -s %d --gpus %d on the kitchen stand-in (.flxs), best of 2 processes; "
+                        "time = render + frame combine + tonemap, scene load excluded" % (spp, n_gpus)}
+    except Exception as e:
+        return {"error": str(e)[-300:]}
+    finally:
+        import shutil
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+# ---------------------------------------------------------------------------------------------------
 # GPU arm
-def recorded_traffic():
-    """DRAM bytes per launch of the traversal kernel from the committed ncu --set full capture (profiles/traffic.json);
-    None when there is no capture for this pool size."""
+TRAVERSAL_SOURCES = ("flx_trace.cu", "flx_bvh.cuh", "flx_math.cuh", "flx_internal.h")
+
+
+def kernel_source_sha1():
+    """Hash of the sources the traversal kernels are built from: profiles/traffic.json records it when a capture is
+    taken (tools/profile_round.sh), and a capture whose hash differs from the tree's is refused (.git does not travel)."""
+    import hashlib
+    h = hashlib.sha1()
+    for name in TRAVERSAL_SOURCES:
+        with open(os.path.join(ROOT, "fluctus_b200", "csrc", name), "rb") as f:
+            h.update(f.read())
+    with open(os.path.join(ROOT, "fluctus_b200", "csrc", "Makefile")) as f:  # the compiler flags, not the file list
+        h.update("".join(l for l in f if l.startswith("NVFLAGS") or l.startswith("  -Xcompiler")).encode())
+    return h.hexdigest()[:12]
+
+
+def recorded_traffic(which=None):
+    """DRAM bytes per launch from the committed `ncu --set full` capture (profiles/traffic.json): the traversal launch of
+    the render (which=None) or the cfg5 ray-cast kernel (which="raycast").  Returns (GB or None, dict of provenance);
+    the figure is RECORDED, not measured in this run, and is dropped when the kernels have changed since the capture."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        if int(t.get("num_tasks", 0)) == NUM_TASKS:
-            extra = {k: t[k] for k in ("issue_slots_busy_pct", "lanes_per_instruction", "l1_hit_pct", "l2_hit_pct") if k in t}
-            return t["dram_bytes_per_launch"] / 1e9, t["source"], extra
-    except (OSError, ValueError, KeyError):
-        pass
-    return None, None, {}
+    except (OSError, ValueError):
+        return None, {"traffic_state": "no capture"}
+    rec = t.get("raycast") if which == "raycast" else t
+    if not rec:
+        return None, {"traffic_state": "no capture"}
+    info = {"traffic_source": rec.get("source"), "traffic_kernel_sha1": t.get("kernel_source_sha1"), "traffic_kind": "recorded"}
+    if t.get("kernel_source_sha1") != kernel_source_sha1():
+        info["traffic_state"] = "stale: the traversal sources changed since the capture (now %s)" % kernel_source_sha1()
+        return None, info
+    if which is None and int(t.get("num_tasks", 0)) != NUM_TASKS:
+        info["traffic_state"] = "capture taken with another pool size"
+        return None, info
+    info["traffic_state"] = "current"
+    info["ncu"] = {k: rec[k] for k in ("issue_slots_busy_pct", "lanes_per_instruction", "l1_hit_pct", "l2_hit_pct") if k in rec}
+    return rec["dram_bytes_per_launch"] / 1e9, info
 
 
 def traversal_bytes(cnt, rays=None, any_hit=False):
@@ -374,13 +543,10 @@ def run_raycast(dev, rank, world, teapot, peak_gbs, steps, warmup, check):
                        "hit_fraction": cnt["hits"] / max(cnt["rays"], 1), "algorithmic_bytes": per_ray},
            "roofline": {"bound": "hbm", "kernel": "k_trace_batch", "achieved": achieved, "peak": peak_gbs, "unit": "GB/s",
                         "frac": achieved / peak_gbs, "traffic": None, "kernel_ms": out["kernel_ms"]}}
-    try:  # DRAM bytes per launch from the committed ncu --set full capture of this kernel (same batch, same scene)
-        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("raycast")
-        if t and int(t.get("rays", 0)) == n:
-            res["roofline"].update({"traffic": t["dram_bytes_per_launch"] / 1e9, "traffic_unit": "GB per launch (DRAM read + write)",
-                                    "traffic_source": t["source"]})
-    except (OSError, ValueError, KeyError):
-        pass
+    rc_gb, rc_info = recorded_traffic("raycast")
+    res["roofline"].update({"traffic": rc_gb, "traffic_unit": "GB per launch (DRAM read + write)"}, **rc_info)
+    if rc_gb:
+        res["roofline"]["dram_frac"] = rc_gb / (out["kernel_ms"] * 1e-3) / peak_gbs
     keep = None
     if check and rank == 0:  # parity sample against the oracle (checker only; tests/ hold the full 2^24 comparison) + CPU rate
         from oracle import pyoracle, refcl
@@ -409,7 +575,7 @@ def run_ours(args):
     import torch.distributed as dist
     import fluctus_b200 as fx
     from fluctus_b200.context import BUF_PREVIEW, STAGE_EXT, STAGE_SHADOW, STAGE_LOGIC, STAGE_RAYGEN, STAGE_MATERIALS
-    from fluctus_b200.multi_gpu import allreduce_pixels, pixels_tensor
+    from fluctus_b200.multi_gpu import pixels_tensor, reduce_pixels
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -444,11 +610,12 @@ def run_ours(args):
         c.render(ITERS_PER_STEP)
         tot = None
         if world > 1:
-            tot = c.getRenderTotals()              # before the reduce: totals are per rank
-            allreduce_pixels(pix)                  # ONE all-reduce of the accumulation buffer per frame
-        c.enqueuePostprocessKernel()
-        if host_io:
-            c.readPixels(BUF_PREVIEW, out=h_frame_np)  # tonemapped frame -> pinned host memory (synchronises)
+            tot = c.getRenderTotals()              # this rank's totals (synchronises; the reduce below moves pixels only)
+            reduce_pixels(pix, dst=0)              # ONE NCCL reduce of the accumulation buffer per frame, into the root
+        if rank == 0:                              # the frame exists on the root only: it alone tonemaps and reads back,
+            c.enqueuePostprocessKernel()           # the other ranks go straight on to the next frame's reset
+            if host_io:
+                c.readPixels(BUF_PREVIEW, out=h_frame_np)  # tonemapped frame -> pinned host memory (synchronises)
         return tot if tot is not None else c.getRenderTotals()
 
     def timed(host_io, steps, with_events):
@@ -484,6 +651,35 @@ def run_ours(args):
         return dict(ms=float(ms.item()), samples=float(agg[0]), ext=float(agg[1]), shadow=float(agg[2]), primary=float(agg[3]),
                     local=tot, launches=c.launchCount() - l0, stage=stage, t0=t0, t1=t1)
 
+    def strong_scaling(total_spp=256):
+        """cfg4 as a FIXED budget: 256 spp at 1080p split spp/G over the ranks (shard_plan; the reference's stop rule
+        counts regenerated paths, src/tracer.cpp:713,773), one reduce into rank 0, tonemap.  Time to completion, max
+        over ranks; work still in flight when a rank reaches its share is the cost of the split."""
+        from fluctus_b200.multi_gpu import shard_plan
+        share = shard_plan(rank, world, NUM_TASKS, n_px, spp=total_spp)["spp"]
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        tot = tr.render(spp=share, batch=8) if share > 0 else c.getRenderTotals()
+        if world > 1:
+            reduce_pixels(pix, dst=0)
+        if rank == 0:
+            c.enqueuePostprocessKernel()
+        e1.record(stream)
+        torch.cuda.synchronize(dev)
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        done = torch.tensor([float(tot["samples"])], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dist.all_reduce(done, op=dist.ReduceOp.SUM)
+        sec = float(ms.item()) * 1e-3
+        return {"spp": total_spp, "spp_per_gpu": share, "seconds": sec, "budget_samples": total_spp * n_px,
+                "msamples_per_s": total_spp * n_px / sec / 1e6, "samples_traced": float(done.item()),
+                "scaling": "strong", "what": "time to %d spp at 1920x1080 with the budget split spp/G, one reduce, tonemap on rank 0; "
+                                             "max over ranks" % total_spp}
+
     clocks = ClockSampler(local) if rank == 0 else None
     for _ in range(max(args.warmup, 1)):
         frame(False)
@@ -510,16 +706,42 @@ def run_ours(args):
     trace_achieved = (ext_bytes + shw_bytes) / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else 0.0
     stage_ms = {("trace" if k == "ext" else k): s[0] for k, s in r["stage"].items() if k not in ("shadow", "raygen") or s[0] > 0}
     stage_sum = sum(stage_ms.values())
-    traffic_gb, traffic_src, traffic_extra = recorded_traffic()
+    traffic_gb, traffic_info = recorded_traffic()
+    # whole-step roofline (SURVEY.md §8d "Msamples/s roofline fraction = sum of stage bytes / t / peak"), per rank, from the
+    # device totals of the timed region: logic reads 100 B of every path every iteration, + 76 B when a NEE sample
+    # resolves (~ one per shadow ray), + 56 B on terminate, + 292 B on continue; raygen 188 B per restarted path;
+    # materials 272 B per shaded path (every extension ray that is not a restart); traversal as above; reset, tonemap.
+    lt = v["local"]
+    shaded = max(lt["extension"] - lt["primary"], 0)
+    ext_b, _ = traversal_bytes(cnt["ext"], rays=lt["extension"])
+    shw_b, _ = traversal_bytes(cnt["shadow"], rays=lt["shadow"], any_hit=True)
+    stage_bytes = {
+        "logic": 100.0 * NUM_TASKS * ITERS_PER_STEP * args.steps + 76.0 * lt["shadow"] + 56.0 * lt["primary"] + 292.0 * shaded,
+        "raygen": 188.0 * lt["primary"], "materials": 272.0 * shaded, "trace": ext_b + shw_b,
+        "reset_tonemap": args.steps * (152.0 * NUM_TASKS + (52.0 + 32.0) * n_px)}
+    step_bytes = sum(stage_bytes.values())
+    step_gbs = step_bytes / (v["ms"] * 1e-3) / 1e9
 
+    strong = strong_scaling() if not args.no_strong_scaling else None
     raycast = None
     if not args.no_raycast:
         raycast, keep = run_raycast(dev, rank, world, teapot, peak, max(args.steps // 2, 3), args.warmup, check=(world == 1))
     else:
         keep = None
-    cpu = ref_cl = None
+    cpu = ref_cl = configs = headless = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline(scene, env, settings)
+    if rank == 0 and world == 1 and not args.no_configs:
+        try:
+            configs = run_configs(dev, stream, teapot, env)
+        except Exception as e:  # a bonus block never costs the bench line
+            configs = {"error": str(e)[-300:]}
+    if world > 1:
+        dist.barrier()  # every rank's timed work is over before rank 0 hands all GPUs to the C++ host
+    if rank == 0 and not args.no_headless:
+        headless = run_headless_cpp(scene, env, settings, world)
+    if world > 1:
+        dist.barrier()
     if rank == 0 and world == 1 and not args.no_reference_opencl:
         tr.close()  # free our pools first: the reference's 2^22-path state is another 1.1 GB + the cfg5 tree in its own layout
         tr = None
@@ -539,22 +761,29 @@ def run_ours(args):
             "e2e": {"value": h["samples"] / (h["ms"] * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": h["ms"] / args.steps,
                     "h2d_bytes_per_step": 256, "d2h_bytes_per_step": n_px * 16 + 48},
             "gpu_launches": int(v["launches"]),
-            "roofline": {"bound": "hbm", "kernel": "k_ext_shadow (extension closest-hit + shadow any-hit traversal of one iteration, one persistent launch)",
-                         "achieved": trace_achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                         "frac": trace_achieved / peak, "traffic": traffic_gb, "traffic_unit": "GB per launch (DRAM read + write)",
-                         "traffic_source": traffic_src, "ncu": traffic_extra,
-                         "algorithmic_gb_per_launch": (ext_bytes + shw_bytes) / max(ext_n, 1) / 1e9,
-                         "note": "the tree of this scene (37 MB) is served from L1/L2: DRAM traffic is a fraction of the algorithmic "
-                                 "bytes (so achieved can exceed the HBM peak) and the kernel is bound by instruction issue, not by HBM "
-                                 "(profiles/r1l_k_ext_shadow_full.md)",
-                         "launches": int(ext_n), "avg_launch_ms": ext_ms / max(ext_n, 1),
-                         "algorithmic_bytes_per_ray": {"extension": ext_per_ray, "shadow": shw_per_ray},
-                         "rays_per_launch": {"extension": r["local"]["extension"] / max(ext_n, 1), "shadow": r["local"]["shadow"] / max(ext_n, 1)},
-                         "share_of_step": ext_ms / stage_sum if stage_sum else None,
-                         "timed_in": "the same K frames repeated launch by launch right after the graph-replayed region, "
-                                     "CUDA events around every stage launch on the context's stream"},
+            "roofline": dict({
+                "bound": "issue", "bound_per_contract": "hbm",
+                "kernel": "k_ext_shadow (extension closest-hit + shadow any-hit traversal of one iteration, one persistent launch)",
+                "achieved": trace_achieved, "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": trace_achieved / peak,
+                "frac_is": "ALGORITHMIC bytes (SURVEY.md 8d: every node / triangle fetch counted, cache hits not subtracted) / kernel time / HBM "
+                           "peak.  This scene's tree (37 MB) is served from L1/L2, so the figure can exceed 1 and is NOT an HBM utilisation: "
+                           "dram_frac is.  The kernel is bound by instruction issue at partial lane occupancy (ncu block); the HBM-facing "
+                           "traversal figure of the metric is raycast.roofline",
+                "traffic": traffic_gb, "traffic_unit": "GB per launch (DRAM read + write)",
+                "dram_frac": (traffic_gb / (ext_ms / max(ext_n, 1) * 1e-3) / peak) if traffic_gb and ext_ms > 0 else None,
+                "algorithmic_gb_per_launch": (ext_bytes + shw_bytes) / max(ext_n, 1) / 1e9,
+                "launches": int(ext_n), "avg_launch_ms": ext_ms / max(ext_n, 1),
+                "algorithmic_bytes_per_ray": {"extension": ext_per_ray, "shadow": shw_per_ray},
+                "rays_per_launch": {"extension": r["local"]["extension"] / max(ext_n, 1), "shadow": r["local"]["shadow"] / max(ext_n, 1)},
+                "share_of_step": ext_ms / stage_sum if stage_sum else None,
+                "timed_in": "the same K frames repeated launch by launch right after the graph-replayed region, "
+                            "CUDA events around every stage launch on the context's stream"}, **traffic_info),
+            "step_roofline": {"bound": "hbm", "achieved": step_gbs, "peak": peak, "unit": "GB/s", "frac": step_gbs / peak,
+                              "what": "sum of the stages' algorithmic bytes (SURVEY.md 8d) of the timed region on one rank / its time",
+                              "gb_per_step": {k: b / args.steps / 1e9 for k, b in stage_bytes.items()}},
             "stage_ms_per_step": {k: t / args.steps for k, t in stage_ms.items()},
             "events_pass_ms_per_step": r["ms"] / args.steps,
+            "strong_scaling": strong, "configs": configs, "headless_cpp": headless,
             "clocks": clk, "cpu_baseline": cpu, "raycast": raycast, "reference_opencl": ref_cl,
         }
         emit(line)
@@ -584,6 +813,9 @@ def main():
     ap.add_argument("--no-raycast", action="store_true", help="skip the cfg5 ray-cast microbench")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-reference-opencl", action="store_true", help="skip timing the reference's kernels through OpenCL")
+    ap.add_argument("--no-configs", action="store_true", help="skip the cfg1/cfg2/cfg3 rows (BASELINE.md 4)")
+    ap.add_argument("--no-headless", action="store_true", help="skip the C++ host (fluctus_headless) leg")
+    ap.add_argument("--no-strong-scaling", action="store_true", help="skip the fixed 256-spp budget record")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON result: libraries that write to fd 1 on their own (NCCL prints its
     # version banner there when NCCL_DEBUG is set) are sent to stderr for the duration of the run.

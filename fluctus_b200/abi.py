@@ -108,3 +108,23 @@ def state_field(state64, name):
     if name in ("i", "areaLightHit", "matId"):
         out = raw.view(np.int32)
     return out[0] if w == 1 else out.T
+
+
+def state_record(params):
+    """The viewer's state file data/states/state_<hash>.dat as Tracer::iterateStateItems writes it (src/tracer.cpp:996-1054):
+    44 little-endian words — camera rotation / speed (viewer-only, zero here), fov, focalDist, apertureSize, dir, pos,
+    right, up, area light N / pos / right / up / E / size, envMapStrength, maxBounces, useAreaLight, useEnvMap, sampleExpl,
+    sampleImpl, useRoulette, exposure, tonemap operator.  `fluctus_headless --load-state` reads it."""
+    r = params[0] if getattr(params, "ndim", 0) else params
+    f = np.zeros(44, np.float32)
+    u = f.view(np.uint32)
+    cam, al = r["camera"], r["areaLight"]
+    f[3], f[4], f[5] = cam["fov"], cam["focalDist"], cam["apertureSize"]
+    f[6:9], f[9:12], f[12:15], f[15:18] = cam["dir"][:3], cam["pos"][:3], cam["right"][:3], cam["up"][:3]
+    f[18:21], f[21:24], f[24:27], f[27:30], f[30:33] = al["N"][:3], al["pos"][:3], al["right"][:3], al["up"][:3], al["E"][:3]
+    f[33], f[34], f[35] = al["size"][0], al["size"][1], r["envMapStrength"]
+    u[36], u[37], u[38], u[39], u[40], u[41] = (r["maxBounces"], r["useAreaLight"], r["useEnvMap"], r["sampleExpl"],
+                                                r["sampleImpl"], r["useRoulette"])
+    f[42] = r["exposure"]
+    u[43] = r["tmOperator"]
+    return f

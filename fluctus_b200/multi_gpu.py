@@ -70,6 +70,16 @@ def allreduce_pixels(pixels, group=None):
     return pixels
 
 
+def reduce_pixels(pixels, dst=0, group=None):
+    """Sum the accumulation buffers of all ranks INTO rank `dst` (one NCCL reduce): for frames that only the root
+    tonemaps and reads back.  The other ranks' buffers keep their own samples and they may start the next frame at once."""
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return pixels
+    dist.reduce(pixels, dst=dst, op=dist.ReduceOp.SUM, group=group)
+    return pixels
+
+
 def reduce_frames(contexts):
     """Several CudaContexts in THIS process, one per GPU (the layout the C++ host uses for `--gpus N`): sum their
     accumulation buffers with the peer-memory kernel of csrc/flx_multi.cu (flx_reduce_frames) — the total ends up

@@ -189,3 +189,40 @@ def kitchen_standin(teapot, grid=(10, 3, 4), seed=7):
                 light_pos=(0.0, 5.95, -1.0), light_n=(0.0, -1.0, 0.0), light_right=(1.0, 0.0, 0.0), light_up=(0.0, 0.0, 1.0),
                 light_e=(40.0, 38.0, 34.0), light_size=(1.5, 1.0))
     return scene, view
+
+
+def conference_standin(cat, grid=(7, 1, 3)):
+    """BASELINE config 3 stand-in (assets/conference/conference.obj, ~330 k triangles, is stripped from the reference
+    snapshot): the reference's egyptcat.obj (16 040 triangles, textured glossy + diffuse + one MIXED material) instanced
+    grid = 7 x 1 x 3 times = 336 840 triangles inside a closed room, lit by one area light under the ceiling — an enclosed,
+    area-light-only scene like the conference room.  Returns (scene dict, camera / light overrides)."""
+    b0, b1 = np.asarray(cat["bounds"][0], np.float32), np.asarray(cat["bounds"][1], np.float32)
+    e = b1 - b0
+    nx, ny, nz = grid
+    sx, sz = float(e[0]) * 1.15, float(e[2]) * 1.3
+    mats = np.concatenate([cat["materials"], _material(abi.BXDF_DIFFUSE, Kd=(0.72, 0.7, 0.66))])
+    wall = len(mats) - 1
+    X0, X1 = float(b0[0]) - 0.6 * sx, float(b0[0]) + (nx - 1) * sx + float(e[0]) + 0.6 * sx
+    Z0, Z1 = float(b0[2]) - 0.6 * sz, float(b0[2]) + (nz - 1) * sz + float(e[2]) + 0.9 * sz
+    Y0, Y1 = float(b0[1]) - 0.01, float(b0[1]) + 2.6 * float(e[1])
+    room = np.concatenate([quad((X0, Y0, Z1), (X1, Y0, Z1), (X1, Y0, Z0), (X0, Y0, Z0), wall),   # floor
+                           quad((X0, Y1, Z0), (X1, Y1, Z0), (X1, Y1, Z1), (X0, Y1, Z1), wall),   # ceiling
+                           quad((X0, Y0, Z0), (X1, Y0, Z0), (X1, Y1, Z0), (X0, Y1, Z0), wall),   # back
+                           quad((X1, Y0, Z1), (X0, Y0, Z1), (X0, Y1, Z1), (X1, Y1, Z1), wall),   # front
+                           quad((X0, Y0, Z1), (X0, Y0, Z0), (X0, Y1, Z0), (X0, Y1, Z1), wall),   # left
+                           quad((X1, Y0, Z0), (X1, Y0, Z1), (X1, Y1, Z1), (X1, Y1, Z0), wall)])  # right
+    rn, ri = build_median_bvh(room)
+    parts = [(room, rn, ri, (0, 0, 0), None)]
+    for i in range(nx):
+        for k in range(nz):
+            parts.append((cat["tris"], cat["nodes"], cat["indices"], (i * sx, 0.0, k * sz), None))
+    tris, nodes, indices = assemble(parts)
+    scene = dict(tris=tris, nodes=nodes, indices=indices, materials=mats,
+                 textures=cat.get("textures", np.zeros(0, TEX_DT)), texels=cat.get("texels", np.zeros(0, np.uint8)))
+    scene["bounds"] = scene_bounds(scene)
+    cx, cz = 0.5 * (X0 + X1), 0.5 * (Z0 + Z1)
+    view = dict(cam_pos=(cx, Y0 + 0.62 * (Y1 - Y0), Z1 - 0.25 * sz), cam_dir=(0.0, -0.28734788, -0.9578263),
+                cam_up=(0.0, 0.9578263, -0.28734788), cam_right=(1.0, 0.0, 0.0), fov=85.0,
+                light_pos=(cx, Y1 - 0.05, cz), light_n=(0.0, -1.0, 0.0), light_right=(1.0, 0.0, 0.0), light_up=(0.0, 0.0, 1.0),
+                light_e=(14.0, 13.5, 12.5), light_size=(0.3 * (X1 - X0), 0.3 * (Z1 - Z0)))
+    return scene, view

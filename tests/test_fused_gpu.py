@@ -13,7 +13,7 @@ import numpy as np
 import pytest
 
 from conftest import cached_scene
-from test_stages_gpu import ALL_FIELDS, MAX_FLIP_FRACTION, _compare_state, _push_oracle_to_gpu, _setup
+from test_stages_gpu import ALL_FIELDS, MAX_COUNT_FRACTION, _compare_state, _push_oracle_to_gpu, _setup
 
 pytestmark = pytest.mark.gpu
 
@@ -70,9 +70,9 @@ def _fused_lockstep(oracle, scene, env, N, W, H, iterations, warm=3, bitstack=Fa
             # restarted paths: integer fields (pixel, seed after the jitter draws, reset flags) exact whatever the tolerance story
             for f in ("pixelIndex", "seed", "pathLen", "lastSpecular", "firstDiffuseHit"):
                 a, b = abi.state_field(g, f)[T], abi.state_field(wf.state(), f)[T]
-                assert (a != b).sum() <= max(2, MAX_FLIP_FRACTION * N), tag + f
+                assert (a != b).sum() <= max(2, MAX_COUNT_FRACTION * N), tag + f
             # device bookkeeping == the host's (tracer.cpp:761-765): totals advance by the oracle's queue lengths
-            tol = max(2, MAX_FLIP_FRACTION * N)
+            tol = max(2, MAX_COUNT_FRACTION * N)
             assert t1["primary"] - t0["primary"] == n, tag + "primary"
             assert abs((t1["extension"] - t0["extension"]) - int(cnt2["extensionQueue"])) <= tol, tag + "extension"
             assert abs((t1["shadow"] - t0["shadow"]) - int(cnt2["shadowQueue"])) <= tol, tag + "shadow"

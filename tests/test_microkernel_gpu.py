@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 from conftest import cached_scene
-from test_stages_gpu import _compare_state, _setup, MAX_FLIP_FRACTION
+from test_stages_gpu import _compare_state, _setup, MAX_COUNT_FRACTION
 
 pytestmark = pytest.mark.gpu
 
@@ -48,7 +48,7 @@ def _lockstep(oracle, scene, env, N, W, H, samples, aov=False, **kw):
             _compare_state(ctx.exportState(), wf.state(), MK_FIELDS, name, allow_flips=not exact)
             s1, g1 = wf.mk_stats().astype(np.int64), ctx.getStats()
             dg = np.array([g1[k] - g0[k] for k in ("primaryRays", "extensionRays", "shadowRays", "samples")])
-            assert np.abs(dg - (s1 - s0)).max() <= max(2, MAX_FLIP_FRACTION * N), (name, dg, s1 - s0)
+            assert np.abs(dg - (s1 - s0)).max() <= max(2, MAX_COUNT_FRACTION * N), (name, dg, s1 - s0)
 
         for s in range(samples):
             stage("s%d raygen" % s, wf.mk_raygen, ctx.enqueueRayGenKernel)

@@ -15,11 +15,17 @@ from conftest import cached_scene
 pytestmark = pytest.mark.gpu
 
 REL_TOL = 1e-5          # stated tolerance for floating-point path state (north_star)
-MAX_FLIP_FRACTION = 2e-3  # paths allowed to diverge through a flipped comparison
+# Paths allowed to differ by more than 1e-4 or in an integer field (a `rand() < F` branch flipped by a last-ulp libm
+# difference).  Set from what the suite observes, as VERDICT r1 asked: the largest fraction over all 286 state
+# comparisons of the GPU suite (per stage, fused iteration, microkernel) is 6e-5 — printed at the end of every run by
+# conftest.pytest_terminal_summary; the limit is 5x that (round 1: 2e-3).
+MAX_FLIP_FRACTION = 3e-4
+MAX_COUNT_FRACTION = 2e-3  # queue lengths / counters compared after a stage (same cause, counted per queue)
 # The env-map lookup is bilinear over a W-texel-wide map: a 1-ulp difference between glibc's and CUDA's
 # atan2f/acosf in the uv coordinate moves the interpolation weight by ~W ulps, so a radiance sample — and
 # the Ei it is added to — can differ by a few 1e-5 relative where neighbouring texels differ strongly.
 # Such paths are counted separately: at most 1 % of the paths may sit between 1e-5 and 1e-4.
+# Observed: at most 0.68 % of the paths of a comparison (the logic stage on an env-map-only teapot scene).
 AMPLIFIED_TOL = 1e-4
 MAX_AMPLIFIED_FRACTION = 1e-2
 OBSERVED = {"flip": 0.0, "amplified": 0.0, "checks": 0}  # largest fractions seen by _compare_state in this session
@@ -111,7 +117,7 @@ def _compare_queues(ctx, wf, names, what):
         qr = set(wf.queue(abi.QUEUES.index(name))[:nr].tolist())
         assert len(qg) == ng, "%s: duplicate entries in %s queue" % (what, name)
         diff = len(qg ^ qr)
-        assert diff <= max(2, MAX_FLIP_FRACTION * wf.N), "%s: %s queue differs in %d entries (%d vs %d)" % (what, name, diff, ng, nr)
+        assert diff <= max(2, MAX_COUNT_FRACTION * wf.N), "%s: %s queue differs in %d entries (%d vs %d)" % (what, name, diff, ng, nr)
 
 
 ALL_FIELDS = ["orig", "dir", "shadowOrig", "shadowDir", "T", "Ei", "lastBsdf", "lastEmission", "lastT", "P", "N", "uvTex",
@@ -158,10 +164,10 @@ def _run_lockstep(oracle, scene, env, N, W, H, iterations, prime=False, spp_pref
             px_g, px_r = ctx.readPixels(BUF_PIXELS), wf.pixels()
             # splat: same samples in a different atomic order -> tiny float reassociation only
             assert np.allclose(px_g, px_r, rtol=1e-4, atol=1e-4), tag + "splat"
-            assert abs(float(px_g[:, 3].sum()) - float(px_r[:, 3].sum())) <= max(2, MAX_FLIP_FRACTION * N)
+            assert abs(float(px_g[:, 3].sum()) - float(px_r[:, 3].sum())) <= max(2, MAX_COUNT_FRACTION * N)
             if int(p[0]["maxSpp"]) > 0:
                 assert np.abs(ctx.readPixels(BUF_SPP).astype(np.int64) - wf.spp().astype(np.int64)).max() <= 1
-                assert abs(int(ctx.getCounters()["splattedSamples"]) - int(wf.counters()["splattedSamples"])) <= max(2, MAX_FLIP_FRACTION * N)
+                assert abs(int(ctx.getCounters()["splattedSamples"]) - int(wf.counters()["splattedSamples"])) <= max(2, MAX_COUNT_FRACTION * N)
 
             _push_oracle_to_gpu(wf, ctx)
             wf.raygen(); ctx.enqueueWfRaygenKernel()
