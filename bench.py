@@ -381,7 +381,7 @@ def run_configs(dev, stream, teapot, env):
     return res
 
 
-def run_headless_cpp(scene, env, settings, n_gpus):
+def run_headless_cpp(scene, env, settings, n_gpus, spp_per_gpu=12):
     """The C++ host (fluctus_headless -> HeadlessTracer -> CudaContext -> the same C-ABI): the benchmark frame rendered by a
     subprocess of rank 0, sample-sharded over n_gpus devices inside that one process, frames combined by
     flx_reduce_frames over NVLink peer memory.  Reports the rate the binary prints (render + combine, without scene load)."""
@@ -399,7 +399,7 @@ def run_headless_cpp(scene, env, settings, n_gpus):
                                "useSeparateQueues": True, "tonemap": 2}}, open(cfg, "w"))
         p = abi.make_render_params(WIDTH, HEIGHT, n_tris=len(scene["tris"]), world_radius=fs.world_radius(scene), **settings)
         abi.state_record(p).tofile(state)
-        spp = 12 * n_gpus  # ~ the samples of one bench frame per GPU
+        spp = spp_per_gpu * n_gpus  # 12 spp per GPU ~ the samples of one bench frame
         best = None
         for _ in range(2):
             r = sp.run([exe, "-x", str(WIDTH), "-y", str(HEIGHT), "-s", str(spp), "--settings", cfg, "--load-state", state,
@@ -736,12 +736,17 @@ def run_ours(args):
             configs = run_configs(dev, stream, teapot, env)
         except Exception as e:  # a bonus block never costs the bench line
             configs = {"error": str(e)[-300:]}
-    if world > 1:
-        dist.barrier()  # every rank's timed work is over before rank 0 hands all GPUs to the C++ host
+    if world > 1 and not args.no_headless:
+        # Every rank's timed work is over before rank 0 hands all GPUs to the C++ host — and the other ranks wait on the
+        # CPU (gloo): an NCCL barrier is a kernel spinning on their GPUs, which the subprocess would have to share
+        # (measured: 158 instead of 353 Msamples/s on 2 GPUs).
+        torch.cuda.synchronize(dev)
+        cpu_group = dist.new_group(backend="gloo")
+        dist.barrier(group=cpu_group)
     if rank == 0 and not args.no_headless:
         headless = run_headless_cpp(scene, env, settings, world)
-    if world > 1:
-        dist.barrier()
+    if world > 1 and not args.no_headless:
+        dist.barrier(group=cpu_group)
     if rank == 0 and world == 1 and not args.no_reference_opencl:
         tr.close()  # free our pools first: the reference's 2^22-path state is another 1.1 GB + the cfg5 tree in its own layout
         tr = None
