@@ -409,10 +409,42 @@ def run_headless_cpp(scene, env, settings, n_gpus, spp_per_gpu=12):
             st = json.loads(r.stdout.strip().splitlines()[-1])
             if best is None or st["msamples_per_s"] > best["msamples_per_s"]:
                 best = st
-        return {"msamples_per_s": best["msamples_per_s"], "seconds": best["seconds"], "samples": best["samples"], "gpus": best["gpus"],
-                "spp": spp, "iterations": best["iterations"], "kernel_launches": best["kernel_launches"],
-                "what": "fluctus_headless -x 1920 -y 1080 -s %d --gpus %d on the kitchen stand-in (.flxs), best of 2 processes; "
-                        "time = render + frame combine + tonemap, scene load excluded" % (spp, n_gpus)}
+        res = {"msamples_per_s": best["msamples_per_s"], "seconds": best["seconds"], "samples": best["samples"], "gpus": best["gpus"],
+               "spp": spp, "iterations": best["iterations"], "kernel_launches": best["kernel_launches"],
+               "what": "fluctus_headless -x 1920 -y 1080 -s %d --gpus %d on the kitchen stand-in (.flxs), best of 2 processes; "
+                       "time = render + frame combine + tonemap, scene load excluded" % (spp, n_gpus)}
+        if n_gpus > 1:
+            # the same job with ONE PROCESS PER GPU and NCCL from the C++ host (flx_comm_init / flx_reduce_pixels, no Python):
+            # n_gpus copies of the binary, rank r on device r; rate = all ranks' samples / the slowest rank's time
+            best = None
+            for attempt in range(2):
+                comm = os.path.join(tmp, "comm_%d.id" % attempt)
+                procs = [sp.Popen([exe, "-x", str(WIDTH), "-y", str(HEIGHT), "-s", str(spp), "--settings", cfg, "--load-state", state,
+                                   "--rank", str(r), "--world", str(n_gpus), "--comm-file", comm, "--out", out, flxs],
+                                  stdout=sp.PIPE, stderr=sp.PIPE, text=True) for r in range(n_gpus)]
+                lines, err = [], None
+                for pr in procs:
+                    try:
+                        o, e = pr.communicate(timeout=300)
+                    except sp.TimeoutExpired:
+                        pr.kill(); o, e = pr.communicate(); err = "timeout"
+                    if pr.returncode != 0:
+                        err = (e or o)[-300:]
+                    else:
+                        lines.append(json.loads(o.strip().splitlines()[-1]))
+                if err:
+                    res["one_process_per_gpu"] = {"error": err}
+                    break
+                sec = max(l["seconds"] for l in lines)
+                tot = sum(l["samples"] for l in lines)
+                cand = {"msamples_per_s": round(tot / sec * 1e-6, 3), "seconds": sec, "samples": tot, "world": n_gpus, "nccl": lines[0]["nccl"],
+                        "what": "%d x fluctus_headless --rank r --world %d: ncclReduce of the accumulation buffers to rank 0 on the render "
+                                "stream (flx_reduce_pixels), best of 2" % (n_gpus, n_gpus)}
+                if best is None or cand["msamples_per_s"] > best["msamples_per_s"]:
+                    best = cand
+            if best is not None and "one_process_per_gpu" not in res:
+                res["one_process_per_gpu"] = best
+        return res
     except Exception as e:
         return {"error": str(e)[-300:]}
     finally:

@@ -41,6 +41,12 @@ SIGNATURES = {
     "flx_render": (I32, [V, U32, I32]),
     "flx_build_lbvh": (I32, [I32, V, SZ, U32, V, SZ, V, V, V]),
     "flx_reduce_frames": (I32, [V, I32]),
+    "flx_comm_unique_id": (I32, [V]),
+    "flx_comm_init": (I32, [V, I32, I32, V]),
+    "flx_comm_destroy": (I32, [V]),
+    "flx_comm_info": (I32, [V, V, V, V]),
+    "flx_allreduce_pixels": (I32, [V]),
+    "flx_reduce_pixels": (I32, [V, I32]),
     "flx_mk_reset": (I32, [V]),
     "flx_mk_raygen": (I32, [V]),
     "flx_mk_next_vertex": (I32, [V]),

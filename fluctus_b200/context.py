@@ -182,6 +182,57 @@ class CudaContext:
         self._check(self.L.flx_trace_closest(self.h, _p(rays), n, _p(hit_i), _p(hit_t), _p(hits)))
         return (hit_i, hit_t, hits) if want_hits else (hit_i, hit_t)
 
+    # ---- one process per GPU: NCCL from the C-ABI (flx_comm.cu; the reference is single-device)
+    @staticmethod
+    def _prefer_bundled_nccl():
+        """The library dlopen()s `libnccl.so.2` at the first flx_comm_* call and takes the copy the process already
+        holds.  In a Python process that copy must be the one torch ships (site-packages/nvidia/nccl): were the
+        system's older libnccl.so.2 loaded first, a later `import torch` would be handed it under the same soname and
+        fail on missing symbols.  So load the bundled one now, unless torch (hence its NCCL) is already in."""
+        import ctypes as C
+        import importlib.util
+        import os
+        import sys
+        if "torch" in sys.modules or os.environ.get("FLX_NCCL_LIB"):
+            return
+        spec = importlib.util.find_spec("nvidia")
+        for root in (list(spec.submodule_search_locations) if spec and spec.submodule_search_locations else []):
+            path = os.path.join(root, "nccl", "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                C.CDLL(path, mode=C.RTLD_GLOBAL)
+                return
+
+    @staticmethod
+    def commUniqueId():
+        """128 bytes drawn by rank 0 and handed to every rank's commInit."""
+        import ctypes as C
+        from ._lib import load
+        CudaContext._prefer_bundled_nccl()
+        buf = C.create_string_buffer(128)
+        if load().flx_comm_unique_id(buf) != 0:
+            raise RuntimeError("flx_comm_unique_id failed: libnccl.so.2 not loadable")
+        return buf.raw
+
+    def commInit(self, rank, world, unique_id):
+        assert len(unique_id) == 128
+        self._prefer_bundled_nccl()
+        self._check(self.L.flx_comm_init(self.h, int(rank), int(world), unique_id))
+
+    def commDestroy(self):
+        self._check(self.L.flx_comm_destroy(self.h))
+
+    def commInfo(self):
+        import ctypes as C
+        r, w, v = C.c_int(0), C.c_int(0), C.c_int(0)
+        self._check(self.L.flx_comm_info(self.h, C.byref(r), C.byref(w), C.byref(v)))
+        return {"rank": r.value, "world": w.value, "nccl_version": v.value}
+
+    def allreducePixels(self):
+        self._check(self.L.flx_allreduce_pixels(self.h))
+
+    def reducePixels(self, root=0):
+        self._check(self.L.flx_reduce_pixels(self.h, int(root)))
+
     def traceClosestStatic(self, rays):
         """flx_trace_closest_static: no allocation on the call path (staging in a static device array, at most
         FLX_STATIC_MAX_RAYS = 262144 rays per call).  No reference counterpart."""

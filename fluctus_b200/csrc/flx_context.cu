@@ -124,6 +124,7 @@ void flx_destroy(flx_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->comm) flx_comm_destroy(ctx);
     drainTimers(ctx);
     invalidateGraph(ctx);
     cudaFree(ctx->dNodes); cudaFree(ctx->dSlots); cudaFree(ctx->dShade);

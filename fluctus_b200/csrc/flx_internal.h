@@ -152,6 +152,7 @@ struct flx_ctx
     flx_render_params params{}; bool paramsSet = false;
     int denoiserAOV = 0; uint32_t seedOffset = 0;
     uint32_t tileRank = 0, tileWorld = 1; // preview sharding: rows y % tileWorld == tileRank belong to this context
+    void *comm = nullptr; int commRank = 0, commWorld = 1; // ncclComm_t of flx_comm_init (flx_comm.cu), one process per GPU
     flx_queue_counters *hCounters = nullptr; // pinned staging for async counter reads
     std::vector<flx_queue_counters *> pendingCounterReads;
 

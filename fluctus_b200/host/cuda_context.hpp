@@ -152,6 +152,23 @@ public:
         }
     }
 
+    // ---- multi-GPU with one process per GPU (new): NCCL over NVLink from the C-ABI (flx_comm.cu) ----------------------
+    // rank 0 draws the id and hands its 128 bytes to the others; commInit is collective
+    static std::vector<unsigned char> commUniqueId()
+    {
+        std::vector<unsigned char> id(FLX_COMM_ID_BYTES);
+        if (flx_comm_unique_id(id.data()) != FLX_OK) throw std::runtime_error("flx_comm_unique_id failed (is libnccl.so.2 on the library path?)");
+        return id;
+    }
+    void commInit(int rank, int world, const std::vector<unsigned char> &id)
+    {
+        if (id.size() != FLX_COMM_ID_BYTES) throw std::runtime_error("commInit: the id must have 128 bytes");
+        check(flx_comm_init(ctx, rank, world, id.data()));
+    }
+    void allreducePixels() { check(flx_allreduce_pixels(ctx)); }   // every rank ends with the summed frame
+    void reducePixels(int root = 0) { check(flx_reduce_pixels(ctx, root)); } // only `root` does
+    int ncclVersion() { int v = 0; check(flx_comm_info(ctx, nullptr, nullptr, &v)); return v; }
+
     // ---- hierarchy build on the GPU (new): stands in for BVH / SBVH construction (src/bvh.cpp, src/sbvh.cpp) -----
     // Returns Node[] (depth-first, left child at index + 1) and fills `indices`: the arrays uploadSceneData takes.
     static std::vector<flx_node> buildHierarchy(const flx_triangle *tris, size_t nTris, std::vector<uint32_t> &indices,

@@ -8,6 +8,7 @@
 //
 //   fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings settings.json] [--env map.hdr] [--bounces N]
 //                    [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D] [--gpus G]
+//                    [--rank R --world W --comm-file F]
 //                    [--benchmark SECONDS [--csv report.csv]] [--load-state F.dat] [--save-state F.dat]
 //                    [--load-accum F.flxa] [--save-accum F.flxa]
 //                    [--out image.ppm|.pfm] [--save-scene out.flxs] scene...
@@ -15,6 +16,11 @@
 // --gpus G      sample-sharded render on devices D..D+G-1 from this one process (one HeadlessTracer and one host
 //               thread per GPU, seeds offset per rank, spp split); the accumulation buffers are summed over NVLink
 //               peer memory (flx_reduce_frames) and rank 0 writes the image.
+// --rank R --world W --comm-file F   the same sharding with ONE PROCESS PER GPU: start W copies of this command with
+//               R = 0..W-1 (device R unless --device is given).  Rank 0 draws an NCCL id and publishes it in file F, the
+//               others wait for it; every rank renders its share and the accumulation buffers are summed with one
+//               ncclReduce to rank 0 on the render stream (flx_comm_init / flx_reduce_pixels), which writes the image.
+//               Every rank prints its own JSON line (its own ray counts); rank 0's names the image.
 // --benchmark S Tracer::runBenchmark's timed loop (src/tracer.cpp:391-565) for S seconds per scene (the reference:
 //               30 s at 1024x1024): CSV rows `scene;time;primary;extension;shadow;total;samples` every half second
 //               to --csv, and the reference's one-line summary per scene on stdout.
@@ -31,12 +37,38 @@
 #include <iostream>
 #include <memory>
 #include <thread>
+#include <unistd.h>
 #include "headless_tracer.hpp"
+
+// rank 0 publishes the NCCL id in `file` (written under a temporary name, then renamed: readers never see half a file);
+// the other ranks poll for it
+static std::vector<unsigned char> exchangeCommId(const std::string &file, int rank, double timeoutSeconds = 120.0)
+{
+    if (rank == 0)
+    {
+        const std::vector<unsigned char> id = flx::CudaContext::commUniqueId();
+        const std::string tmp = file + ".tmp";
+        { std::ofstream f(tmp, std::ios::binary); f.write((const char *)id.data(), (std::streamsize)id.size()); if (!f) throw std::runtime_error("cannot write " + tmp); }
+        if (std::rename(tmp.c_str(), file.c_str()) != 0) throw std::runtime_error("cannot rename " + tmp + " to " + file);
+        return id;
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    for (;;)
+    {
+        std::ifstream f(file, std::ios::binary);
+        std::vector<unsigned char> id(FLX_COMM_ID_BYTES);
+        if (f && f.read((char *)id.data(), (std::streamsize)id.size())) return id;
+        if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > timeoutSeconds)
+            throw std::runtime_error("timed out waiting for rank 0's communicator id in " + file);
+        usleep(20000);
+    }
+}
 
 static void usage()
 {
     std::cerr << "usage: fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings FILE] [--env FILE.hdr] [--bounces N]\n"
                  "                        [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D] [--gpus G]\n"
+                 "                        [--rank R --world W --comm-file F]\n"
                  "                        [--benchmark SECONDS [--csv FILE.csv]] [--load-state F.dat] [--save-state F.dat]\n"
                  "                        [--load-accum F.flxa] [--save-accum F.flxa]\n"
                  "                        [--out FILE.ppm|.pfm] [--save-scene FILE.flxs] scene...\n";
@@ -47,11 +79,11 @@ static bool endsWith(const std::string &s, const std::string &e) { return s.size
 int main(int argc, char **argv)
 {
     flx::Settings settings;
-    int width = -1, height = -1, spp = 32, device = 0, bounces = -1, gpus = 1;
+    int width = -1, height = -1, spp = 32, device = -1, bounces = -1, gpus = 1, rank = 0, world = 1;
     uint32_t iterations = 0, tasks = 0, lbvhLeaf = 0;
     bool useMK = false;
     double benchSeconds = 0.0;
-    std::string out = "output.ppm", saveScene, env, csvFile, loadState, saveState, loadAccum, saveAccum;
+    std::string out = "output.ppm", saveScene, env, csvFile, loadState, saveState, loadAccum, saveAccum, commFile;
     std::vector<std::string> scenes;
     try
     {
@@ -73,6 +105,9 @@ int main(int argc, char **argv)
             else if (a == "--tasks") tasks = (uint32_t)std::stoul(next());
             else if (a == "--lbvh") lbvhLeaf = (uint32_t)std::stoul(next());
             else if (a == "--gpus") gpus = std::stoi(next());
+            else if (a == "--rank") rank = std::stoi(next());
+            else if (a == "--world") world = std::stoi(next());
+            else if (a == "--comm-file") commFile = next();
             else if (a == "--benchmark") benchSeconds = std::stod(next());
             else if (a == "--csv") csvFile = next();
             else if (a == "--load-state") loadState = next();
@@ -91,6 +126,11 @@ int main(int argc, char **argv)
         if (gpus < 1 || gpus > 16) throw std::runtime_error("--gpus 1..16");
         if (benchSeconds < 0.0) throw std::runtime_error("--benchmark needs a positive duration");
         if (gpus > 1 && (benchSeconds > 0.0 || !loadAccum.empty())) throw std::runtime_error("--benchmark / --load-accum run on one GPU");
+        if (world < 1 || world > 64 || rank < 0 || rank >= world) throw std::runtime_error("--rank R --world W with 0 <= R < W <= 64");
+        if (world > 1 && commFile.empty()) throw std::runtime_error("--world needs --comm-file (where rank 0 publishes the NCCL id)");
+        if (world > 1 && (gpus > 1 || benchSeconds > 0.0 || !loadAccum.empty()))
+            throw std::runtime_error("--world (one process per GPU) excludes --gpus / --benchmark / --load-accum");
+        if (device < 0) device = world > 1 ? rank : 0;
         if (bounces >= 0) settings.maxPathDepth = bounces;
         if (env.empty()) env = settings.envMapName;
     }
@@ -130,9 +170,12 @@ int main(int argc, char **argv)
             // the microkernel renderer keeps one task per pixel (mk_raygen.cl:8-9)
             if (useMK && (uint64_t)sceneSettings.wfBufferSize < (uint64_t)width * height) sceneSettings.wfBufferSize = (uint32_t)(width * height);
             // one tracer per GPU: rank r renders the samples of shard r (seed offset r*N, pixel cursor r*w*h/G, spp/G)
-            if (gpus > 1 && sceneSettings.maxSpp > 0) sceneSettings.maxSpp = (sceneSettings.maxSpp + gpus - 1) / gpus;
+            // (--gpus: the shards are this process's tracers; --world: this process is shard `rank` of `world`)
+            const int shards = world > 1 ? world : gpus;
+            auto shardOf = [&](int r) { return world > 1 ? rank : r; };
+            if (shards > 1 && sceneSettings.maxSpp > 0) sceneSettings.maxSpp = (sceneSettings.maxSpp + shards - 1) / shards;
             std::vector<std::unique_ptr<flx::HeadlessTracer>> tracers;
-            for (int r = 0; r < gpus; r++) tracers.emplace_back(new flx::HeadlessTracer(width, height, sceneSettings, device + r, r, gpus));
+            for (int r = 0; r < gpus; r++) tracers.emplace_back(new flx::HeadlessTracer(width, height, sceneSettings, device + r, shardOf(r), shards));
             flx::HeadlessTracer &tracer = *tracers[0];
             for (auto &t : tracers) { t->init(scene); if (!loadState.empty()) t->loadState(loadState); }
             if (!saveState.empty()) tracer.saveState(saveState);
@@ -141,6 +184,13 @@ int main(int argc, char **argv)
                 std::vector<flx::CudaContext *> ctxs;
                 for (auto &tr : tracers) ctxs.push_back(&tr->getClContext());
                 flx::CudaContext::reduceFrames(ctxs);
+            }
+            if (world > 1) // join the communicator; one combine of the still empty frames warms NCCL's channels up and lines the ranks up
+            {
+                flx::CudaContext &c = tracer.getClContext();
+                c.commInit(rank, world, exchangeCommId(commFile + (scenes.size() > 1 ? "." + std::to_string(si) : ""), rank));
+                c.allreducePixels();
+                c.finishQueue();
             }
             const auto t0 = std::chrono::steady_clock::now();
             flx::CudaContext::Totals t{};
@@ -173,7 +223,8 @@ int main(int argc, char **argv)
                         }
                         else
                         {
-                            const uint32_t share = (uint32_t)spp / (uint32_t)gpus + ((uint32_t)r < (uint32_t)spp % (uint32_t)gpus ? 1u : 0u);
+                            const uint32_t ws = (uint32_t)shards, me = (uint32_t)shardOf(r);
+                            const uint32_t share = (uint32_t)spp / ws + (me < (uint32_t)spp % ws ? 1u : 0u);
                             if (!loadAccum.empty())
                             {
                                 tr.render(0, 0); // reset + priming segment, then the checkpoint goes on top
@@ -204,20 +255,26 @@ int main(int argc, char **argv)
                     for (auto &tr : tracers) ctxs.push_back(&tr->getClContext());
                     flx::CudaContext::reduceFrames(ctxs);
                 }
+                if (world > 1) // one ncclReduce on the render stream: rank 0's buffer becomes the frame
+                {
+                    tracer.getClContext().reducePixels(0);
+                    tracer.getClContext().finishQueue();
+                }
             }
-            if (!saveAccum.empty()) tracer.saveAccumulation(saveAccum);
+            if (!saveAccum.empty() && rank == 0) tracer.saveAccumulation(saveAccum);
             const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
             std::string file = out;
             if (scenes.size() > 1) file = out.substr(0, out.rfind('.')) + "_" + std::to_string(si) + out.substr(out.rfind('.'));
-            tracer.saveImage(file);
+            if (rank == 0) tracer.saveImage(file);
             uint64_t launches = 0;
             for (auto &tr : tracers) launches += tr->getClContext().launchCount();
             printf("{\"scene\": \"%s\", \"width\": %d, \"height\": %d, \"triangles\": %zu, \"iterations\": %llu, \"primary\": %llu, "
                    "\"extension\": %llu, \"shadow\": %llu, \"samples\": %llu, \"seconds\": %.4f, \"msamples_per_s\": %.3f, "
-                   "\"mrays_per_s\": %.3f, \"gpus\": %d, \"kernel_launches\": %llu, \"image\": \"%s\"}\n",
+                   "\"mrays_per_s\": %.3f, \"gpus\": %d, \"rank\": %d, \"world\": %d, \"nccl\": %d, \"kernel_launches\": %llu, \"image\": \"%s\"}\n",
                    scenes[si].c_str(), width, height, scene.tris.size(), (unsigned long long)t.iterations, (unsigned long long)t.primary,
                    (unsigned long long)t.extension, (unsigned long long)t.shadow, (unsigned long long)t.samples, sec, t.samples / sec * 1e-6,
-                   (t.primary + t.extension + t.shadow) / sec * 1e-6, gpus, (unsigned long long)launches, file.c_str());
+                   (t.primary + t.extension + t.shadow) / sec * 1e-6, gpus, rank, world, world > 1 ? tracer.getClContext().ncclVersion() : 0,
+                   (unsigned long long)launches, rank == 0 ? file.c_str() : "");
         }
         catch (const std::exception &e)
         {

@@ -146,9 +146,33 @@ int flx_set_traversal(flx_ctx *ctx, int use_bitstack);
  * enabled) element-wise in rank order: afterwards ctxs[0] holds the total — run flx_postprocess / flx_read_pixels
  * on it — and the other buffers are zero, so all contexts may go on accumulating and be combined again.  The sum is
  * a kernel over NVLink peer memory (GPU d combines rows slice d from all N buffers); without peer access the frames
- * are staged through the root.  With one process per GPU use an NCCL all-reduce of flx_device_ptr(ctx,
- * FLX_BUF_PIXELS) instead (fluctus_b200/multi_gpu.py).  Synchronises. */
+ * are staged through the root.  With one process per GPU use flx_allreduce_pixels below.  samplesPerPixel (the
+ * CHECK_SPP budget) stays per context.  Synchronises. */
 int flx_reduce_frames(flx_ctx *const *ctxs, int n);
+
+/* ---- multi-GPU frame combine with ONE PROCESS PER GPU: NCCL over NVLink 5 / NVSwitch (new; SURVEY.md §8b/§8e — the
+ * reference has no collective call site) -----------------------------------------------------------------------
+ * Every rank renders its sample shard of the frame into its own context (same resolution and parameters, seeds offset
+ * with flx_set_options) and once per frame the accumulation buffers are summed:
+ *     rank 0:     flx_comm_unique_id(id)        -> hand the 128 bytes to the other ranks (file, socket, MPI, env ...)
+ *     every rank: flx_comm_init(ctx, rank, world, id)              (collective: returns when all ranks have joined)
+ *     per frame:  flx_render(...); flx_allreduce_pixels(ctx)       every rank ends with the total, or
+ *                 flx_render(...); flx_reduce_pixels(ctx, 0)       only rank 0 does (the other buffers are unchanged:
+ *                                                                   clear them before they go on accumulating)
+ *                 rank 0: flx_postprocess / flx_read_pixels
+ * The collective is ONE grouped NCCL call over float4[w*h] (+ the two denoiser AOV sums when enabled), enqueued on the
+ * context's stream after the render — nothing synchronises; flx_read_pixels / flx_finish do.  samplesPerPixel
+ * (CHECK_SPP's per-pixel budget) is per rank and is not combined.  NCCL is not linked: libnccl.so.2 is dlopen'ed at the
+ * first call, the copy already loaded in the process if there is one (under Python, torch's), and a missing library is
+ * an FLX_ERR_STATE with a message, not a load failure of this library.  flx_destroy destroys the communicator.
+ * flx_comm_info: rank, world (0 = no communicator) and the NCCL version in use (0 = not loaded); any may be NULL. */
+#define FLX_COMM_ID_BYTES 128
+int flx_comm_unique_id(void *id128);
+int flx_comm_init(flx_ctx *ctx, int rank, int world, const void *id128);
+int flx_comm_destroy(flx_ctx *ctx);
+int flx_comm_info(flx_ctx *ctx, int *rank, int *world, int *nccl_version);
+int flx_allreduce_pixels(flx_ctx *ctx);
+int flx_reduce_pixels(flx_ctx *ctx, int root);
 
 /* ---- parallel hierarchy build (new) --------------------------------------------------------
  * Linear BVH (63-bit Morton order + Karras' radix tree, subtrees of <= max_leaf triangles collapsed into one leaf)

@@ -30,6 +30,19 @@ def test_headless_links_the_c_abi_library():
     assert r.returncode == 2
 
 
+def test_headless_one_process_per_gpu_flags():
+    """--rank / --world / --comm-file (NCCL from the C++ host, flx_comm.cu): argument errors are caught before any work."""
+    _need_bin()
+    for args, msg in ((["--world", "2", "s.flxs"], "--comm-file"),
+                      (["--world", "2", "--rank", "2", "--comm-file", "/tmp/x", "s.flxs"], "0 <= R < W"),
+                      (["--world", "2", "--rank", "1", "--comm-file", "/tmp/x", "--gpus", "2", "s.flxs"], "excludes")):
+        r = subprocess.run([BIN] + args, capture_output=True, text=True)
+        assert r.returncode == 2 and msg in r.stderr, (args, r.stderr)
+    # NCCL is not a link-time dependency of the library or the binary (dlopen at the first flx_comm_* call)
+    lib = os.path.join(ROOT, "fluctus_b200", "libfluctus_cuda.so")
+    assert "nccl" not in subprocess.check_output(["ldd", BIN], text=True) + subprocess.check_output(["ldd", lib], text=True)
+
+
 def test_flxs_roundtrip_python(tmp_path, teapot, night_env):
     from fluctus_b200 import scene as fs
     p = str(tmp_path / "t.flxs")
