@@ -602,6 +602,80 @@ def run_raycast(dev, rank, world, teapot, peak_gbs, steps, warmup, check):
     return res, keep
 
 
+def run_lbvh(dev, stream, teapot, scene, env, settings, steps=3):
+    """The hierarchy built on the GPU (flx_build_lbvh: Morton order + radix tree, emitted in the reference's Node[] format)
+    in place of the reference's SBVH: build time, the benchmark frame and the cfg5 ray batch on it.  Same kernels, same
+    timing method as the headline numbers; only the tree differs (rank 0, N=1)."""
+    import torch
+    import fluctus_b200 as fx
+    from fluctus_b200 import CudaContext, scene as fs
+    out = {"max_leaf": 4}
+    # ---- the benchmark frame on the kitchen stand-in
+    fs.build_lbvh(scene, max_leaf=4, device=dev.index)                      # warm-up: context, cub temp sizes
+    t0 = time.perf_counter()
+    lb = fs.build_lbvh(scene, max_leaf=4, device=dev.index)
+    out["kitchen"] = {"triangles": int(len(scene["tris"])), "build_s": round(time.perf_counter() - t0, 4),
+                      "nodes": int(len(lb["nodes"])), "depth": lb["lbvh_depth"], "sbvh_nodes": int(len(scene["nodes"]))}
+    tr = fx.Tracer(WIDTH, HEIGHT, num_tasks=NUM_TASKS, device=dev.index, stream=stream.cuda_stream, **settings)
+    tr.init(lb, env)
+    tr.clctx.setTraversal(BITSTACK)
+    c = tr.clctx
+
+    def frame():
+        c.setPixelIndex(0)
+        c.render(0, reset=True)
+        c.render(ITERS_PER_STEP)
+        c.enqueuePostprocessKernel()
+        return c.getRenderTotals()
+    for _ in range(2):
+        frame()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    e0.record(stream)
+    samples = 0
+    for _ in range(steps):
+        samples += frame()["samples"]
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1)
+    out["kitchen"].update({"msamples_per_s": samples / ms / 1e3, "ms_per_step": ms / steps, "steps": steps})
+    tr.close()
+    # ---- cfg5: 2^24 incoherent rays, 10.1 M triangles
+    grid = fs.replicate_grid(teapot, (15, 15, 14), (2.2, 1.1, 1.4))
+    t0 = time.perf_counter()
+    glb = fs.build_lbvh(grid, max_leaf=4, device=dev.index)
+    t_build = time.perf_counter() - t0
+    n = 1 << 24
+    rays = fs.bench_rays(n, grid["bounds"])
+    ctx = CudaContext(num_tasks=1024, device=dev.index, stream=stream.cuda_stream)
+    ctx.uploadSceneData(glb)
+    ctx.setTraversal(BITSTACK and glb["lbvh_depth"] < 31)
+    d_rays = torch.from_numpy(rays).to(dev)
+    d_i = torch.empty(n, dtype=torch.int32, device=dev)
+    d_t = torch.empty(n, dtype=torch.float32, device=dev)
+    for _ in range(3):
+        ctx.traceClosestDevice(d_rays.data_ptr(), n, d_i.data_ptr(), d_t.data_ptr())
+    torch.cuda.synchronize(dev)
+    e0.record(stream)
+    for _ in range(steps):
+        ctx.traceClosestDevice(d_rays.data_ptr(), n, d_i.data_ptr(), d_t.data_ptr())
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    ms = e0.elapsed_time(e1) / steps
+    ctx.setTraceCounting(True)
+    ctx.traceClosestDevice(d_rays.data_ptr(), n, d_i.data_ptr(), d_t.data_ptr())
+    cnt = ctx.traceCounters()["batch_closest"]
+    ctx.setTraceCounting(False)
+    out["cfg5"] = {"triangles": int(len(grid["tris"])), "build_s": round(t_build, 3), "nodes": int(len(glb["nodes"])),
+                   "depth": glb["lbvh_depth"], "sbvh_nodes": int(len(grid["nodes"])), "mrays_per_s": n / ms / 1e3, "ms": ms,
+                   "per_ray": {"inner_nodes": cnt["inner"] / max(cnt["rays"], 1), "triangle_tests": cnt["tri"] / max(cnt["rays"], 1),
+                               "hit_fraction": cnt["hits"] / max(cnt["rays"], 1)}}
+    ctx.close()
+    out["what"] = ("flx_build_lbvh (max_leaf 4) replaces the scene's SBVH; build_s = host call incl. H2D of the triangles and D2H of "
+                   "the tree; frame and ray batch timed as the headline numbers (CUDA events, device-resident inputs)")
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -768,6 +842,12 @@ def run_ours(args):
             configs = run_configs(dev, stream, teapot, env)
         except Exception as e:  # a bonus block never costs the bench line
             configs = {"error": str(e)[-300:]}
+    lbvh = None
+    if rank == 0 and world == 1 and not args.no_lbvh:
+        try:
+            lbvh = run_lbvh(dev, stream, teapot, scene, env, settings)
+        except Exception as e:
+            lbvh = {"error": str(e)[-300:]}
     if world > 1 and not args.no_headless:
         # Every rank's timed work is over before rank 0 hands all GPUs to the C++ host — and the other ranks wait on the
         # CPU (gloo): an NCCL barrier is a kernel spinning on their GPUs, which the subprocess would have to share
@@ -820,7 +900,7 @@ def run_ours(args):
                               "gb_per_step": {k: b / args.steps / 1e9 for k, b in stage_bytes.items()}},
             "stage_ms_per_step": {k: t / args.steps for k, t in stage_ms.items()},
             "events_pass_ms_per_step": r["ms"] / args.steps,
-            "strong_scaling": strong, "configs": configs, "headless_cpp": headless,
+            "strong_scaling": strong, "configs": configs, "lbvh": lbvh, "headless_cpp": headless,
             "clocks": clk, "cpu_baseline": cpu, "raycast": raycast, "reference_opencl": ref_cl,
         }
         emit(line)
@@ -853,6 +933,7 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="skip the cfg1/cfg2/cfg3 rows (BASELINE.md 4)")
     ap.add_argument("--no-headless", action="store_true", help="skip the C++ host (fluctus_headless) leg")
     ap.add_argument("--no-strong-scaling", action="store_true", help="skip the fixed 256-spp budget record")
+    ap.add_argument("--no-lbvh", action="store_true", help="skip the GPU-built hierarchy (flx_build_lbvh) rates")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON result: libraries that write to fd 1 on their own (NCCL prints its
     # version banner there when NCCL_DEBUG is set) are sent to stderr for the duration of the run.

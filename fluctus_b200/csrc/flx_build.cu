@@ -21,6 +21,7 @@
 // and one from the reference's builder agree on t bit for bit and on the triangle except for exact ties.
 #include <cub/device/device_radix_sort.cuh>
 #include "flx_internal.h"
+#include "flx_bvh.cuh" // FLX_STACK_SIZE
 
 #define FLX_BUILD_THREADS 256
 
@@ -263,5 +264,11 @@ extern "C" int flx_build_lbvh(int device, const flx_triangle *tris, size_t n_tri
     int depth = 0;
     BUILD_CUDA(cudaMemcpy(&depth, dMisc + 6, sizeof(int), cudaMemcpyDeviceToHost));
     if (depth_out) *depth_out = (uint32_t)depth;
+    // k_emit counts edges below the root; the traversal's stack holds one entry per LEVEL.  A radix tree over 63 Morton
+    // bits + the index tie-break can reach ~95 levels on inputs with many (near-)coincident centroids — instanced or
+    // duplicated geometry — which flx_upload_scene would refuse: say so here, where the caller can still react.
+    if (depth + 1 > FLX_STACK_SIZE)
+        return flx_fail(nullptr, FLX_ERR_ARG, "flx_build_lbvh: the hierarchy is " + std::to_string(depth + 1) + " levels deep (coincident centroids?) and the "
+                        "traversal holds " + std::to_string(FLX_STACK_SIZE) + " (flx_upload_scene would refuse it): build with a larger max_leaf");
     return FLX_OK;
 }

@@ -181,6 +181,9 @@ int flx_upload_scene(flx_ctx *ctx, const flx_triangle *tris, size_t n_tris, cons
     for (size_t i = 0; i < n_textures; i++)
         if ((size_t)textures[i].offset + (size_t)textures[i].width * textures[i].height * 4 > texel_bytes)
             return flx_fail(ctx, FLX_ERR_ARG, "flx_upload_scene: texture descriptor outside texel data");
+    for (size_t i = 0; i < n_textures; i++) // readTexel (flx_shade.cuh) loads a texel as one uchar4; the reference's loader packs RGBA8, offsets are multiples of 4
+        if (textures[i].offset & 3u)
+            return flx_fail(ctx, FLX_ERR_ARG, "flx_upload_scene: texture offset " + std::to_string(textures[i].offset) + " is not a multiple of 4 (texels are RGBA8 words)");
 
     cudaFree(ctx->dMaterials); cudaFree(ctx->dTextures); cudaFree(ctx->dTexels); cudaFree(ctx->dTris160);
     ctx->dMaterials = nullptr; ctx->dTextures = nullptr; ctx->dTexels = nullptr; ctx->dTris160 = nullptr;

@@ -15,7 +15,9 @@ import numpy as np
 
 
 def shard_plan(rank, world_size, num_tasks, num_pixels, spp=None):
-    """Decorrelation parameters of one rank: dict(seed_offset, cursor_start, spp)."""
+    """Decorrelation parameters of one rank: dict(seed_offset, cursor_start, spp).  A per-pixel budget (maxSpp > 0,
+    CHECK_SPP) is per context and NOT combined by reduce_frames / allreduce_pixels: give every rank ceil(maxSpp / world)
+    (Tracer(world_size=...) and fluctus_headless do), or N ranks deliver N * maxSpp samples per pixel."""
     rank, world_size = int(rank), int(world_size)
     if not (0 <= rank < world_size):
         raise ValueError("rank %d outside world of %d" % (rank, world_size))

@@ -18,6 +18,10 @@ class Tracer:
         self.rank, self.world_size = int(rank), int(world_size)
         self.clctx = CudaContext(num_tasks, device, stream)  # name kept from the reference (tracer.hpp:131)
         self.settings = dict(settings)
+        # CHECK_SPP's per-pixel budget (samplesPerPixel) stays per context — the frame combine sums pixels only — so a
+        # rank of a sample-sharded render takes its share of maxSpp, as fluctus_headless does (ceil(maxSpp / world))
+        if self.world_size > 1 and int(self.settings.get("max_spp", 0)) > 0:
+            self.settings["max_spp"] = -(-int(self.settings["max_spp"]) // self.world_size)
         self.params = make_render_params(width, height, **self.settings)
         self.iteration = 0
         self.stats = dict(primaryRays=0, extensionRays=0, shadowRays=0, samples=0)  # CLContext::statsAsync

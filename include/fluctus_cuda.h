@@ -180,7 +180,9 @@ int flx_reduce_pixels(flx_ctx *ctx, int root);
  * child at index + 1 (src/bvhnode.hpp:50-59) and the index list its leaves point into — i.e. a drop-in for the
  * arrays BVH / SBVH (src/bvh.cpp, src/sbvh.cpp) hand to CLContext::uploadSceneData.  nodes_capacity >= 2*n_tris - 1
  * always suffices; *n_nodes_out receives the number written; indices_out has n_tris entries; *depth_out (optional)
- * the depth of the tree (flx_upload_scene refuses hierarchies deeper than its 64-entry traversal stack).
+ * the depth of the tree in edges below the root.  A tree of more than 64 LEVELS — possible with many coincident
+ * centroids: Morton bits + index tie-break — is an FLX_ERR_ARG here (flx_upload_scene's traversal stack holds 64
+ * entries and would refuse it): rebuild with a larger max_leaf.
  * Stateless and synchronous.  No CPU fallback. */
 int flx_build_lbvh(int device, const flx_triangle *tris, size_t n_tris, uint32_t max_leaf,
                    flx_node *nodes_out, size_t nodes_capacity, size_t *n_nodes_out, uint32_t *indices_out, uint32_t *depth_out);

@@ -90,6 +90,50 @@ def test_lbvh_degenerate_inputs(oracle, teapot):
     ctx.close()
 
 
+def test_lbvh_too_deep_for_the_traversal_stack_is_refused_at_build_time(oracle, teapot):
+    """A chain of 52 Morton levels (one triangle per top bit) ending in 16384 coincident triangles (index tie-break, 14
+    more levels) is deeper than the 64-entry stack: flx_build_lbvh says so itself instead of handing out a hierarchy
+    that flx_upload_scene refuses; a larger max_leaf collapses the coincident run and the build goes through."""
+    from fluctus_b200 import CudaContext, FluctusError, scene as fs
+    t0 = teapot["tris"][:1].copy()
+    shape = t0["v"][0, :, 0, :3] - t0["v"][0, :, 0, :3].mean(0)
+    shape *= np.float32(0.05 / np.abs(shape).max())
+    pos = [np.zeros(3, np.float32)] * 16384
+    for j in range(11, 63):
+        c = np.zeros(3, np.float32); c[j % 3] = np.float32(2.0 ** (j // 3))
+        pos.append(c)
+    tris = np.repeat(t0, len(pos))
+    tris["v"][:, :, 0, :3] = shape[None] + np.stack(pos)[:, None, :]
+    s = dict(teapot); s["tris"] = tris
+    with pytest.raises(FluctusError) as e:
+        fs.build_lbvh(s, max_leaf=1)
+    assert "levels deep" in str(e.value) and "max_leaf" in str(e.value)
+    lb = fs.build_lbvh(s, max_leaf=255)
+    assert lb["lbvh_depth"] + 1 <= 64
+    ctx = CudaContext(num_tasks=64)
+    rays = _rays_inside(lb, 512, 5)
+    _check_closest(ctx, oracle, lb, rays)
+    ctx.close()
+
+
+def test_upload_rejects_misaligned_texture_offsets(teapot):
+    """readTexel loads RGBA8 texels as words (flx_shade.cuh): an offset that is not a multiple of 4 is refused at upload
+    instead of faulting in the shading kernels."""
+    from fluctus_b200 import CudaContext, FluctusError
+    from fluctus_b200.abi import TEX_DT
+    s = dict(teapot)
+    s["textures"] = np.array([(2, 4, 4)], TEX_DT)
+    s["texels"] = np.zeros(2 + 4 * 4 * 4, np.uint8)
+    ctx = CudaContext(num_tasks=64)
+    with pytest.raises(FluctusError) as e:
+        ctx.uploadSceneData(s)
+    assert "multiple of 4" in str(e.value)
+    s["textures"] = np.array([(4, 4, 4)], TEX_DT)
+    s["texels"] = np.zeros(4 + 4 * 4 * 4, np.uint8)
+    ctx.uploadSceneData(s)
+    ctx.close()
+
+
 def test_lbvh_ten_million_triangles(oracle, teapot):
     """cfg5-size input (15x15x14 teapots, 10 098 900 triangles): builds in well under a second of GPU work where the
     reference's single-threaded builder needs minutes; rays agree with the replicated-SBVH hierarchy on t bit for bit."""

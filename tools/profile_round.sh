@@ -8,7 +8,7 @@ TAG=${1:-rX}
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err || exit 1
-CMD="python bench.py --steps 2 --warmup 3 --no-raycast --no-cpu-baseline --no-reference-opencl --no-configs --no-headless --no-strong-scaling"
+CMD="python bench.py --steps 2 --warmup 3 --no-raycast --no-cpu-baseline --no-reference-opencl --no-configs --no-headless --no-strong-scaling --no-lbvh"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_launch.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"k_ext_shadow" --launch-skip 100 -c 1 -o gpurun_out/${TAG}_k_ext_shadow $CMD > gpurun_out/${TAG}_ncu_full.log 2>&1
 tail -2 gpurun_out/${TAG}_ncu_full.log
