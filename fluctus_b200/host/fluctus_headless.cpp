@@ -9,7 +9,8 @@
 //   fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings settings.json] [--env map.hdr] [--bounces N]
 //                    [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D] [--gpus G]
 //                    [--rank R --world W --comm-file F]
-//                    [--benchmark SECONDS [--csv report.csv]] [--load-state F.dat] [--save-state F.dat]
+//                    [--benchmark SECONDS [--csv report.csv]] [--benchmark-file F.bm.json]
+//                    [--load-state F.dat] [--save-state F.dat]
 //                    [--load-accum F.flxa] [--save-accum F.flxa]
 //                    [--out image.ppm|.pfm] [--save-scene out.flxs] scene...
 //
@@ -24,6 +25,14 @@
 // --benchmark S Tracer::runBenchmark's timed loop (src/tracer.cpp:391-565) for S seconds per scene (the reference:
 //               30 s at 1024x1024): CSV rows `scene;time;primary;extension;shadow;total;samples` every half second
 //               to --csv, and the reference's one-line summary per scene on stdout.
+// --benchmark-file F.bm.json   Tracer::runBenchmarkFromFile (src/tracer.cpp:567-870): the reference's benchmark description
+//               — {"settings": {...}, "outputFolder": "...", "scenes": [{"file": ..., "outputFile": ..., "settings": {...}}]},
+//               paths relative to the file — parsed by the reference's own Settings::import (built with the reference
+//               tree only).  Per scene: window size, renderer (useWavefront), bounces, lights, camera ... from the
+//               settings, render until maxRenderTime / maxSpp (30 s when neither is given), then
+//               <outputFolder>/<outputFile>.ppm + .pfm (the reference: .png + .hdr), .csv and .txt as the reference writes
+//               them, the summary line and one JSON line on stdout.  Takes no scene arguments.
+// --dump-settings  print the settings in force (after --settings / per scene of --benchmark-file) as JSON and exit: no GPU work.
 // --load-state / --save-state  the reference's data/states/state_<hash>.dat (camera, lights, sampling, tonemap).
 // --load-accum / --save-accum  raw accumulation checkpoint: a progressive render resumes where it stopped.
 //
@@ -64,26 +73,102 @@ static std::vector<unsigned char> exchangeCommId(const std::string &file, int ra
     }
 }
 
+static bool endsWith(const std::string &s, const std::string &e) { return s.size() >= e.size() && s.compare(s.size() - e.size(), e.size(), e) == 0; }
+
 static void usage()
 {
     std::cerr << "usage: fluctus_headless [-x W] [-y H] [-s SPP] [-b] [--settings FILE] [--env FILE.hdr] [--bounces N]\n"
                  "                        [--renderer wavefront|mk] [--tasks N] [--lbvh MAXLEAF] [--iterations N] [--device D] [--gpus G]\n"
                  "                        [--rank R --world W --comm-file F]\n"
-                 "                        [--benchmark SECONDS [--csv FILE.csv]] [--load-state F.dat] [--save-state F.dat]\n"
+                 "                        [--benchmark SECONDS [--csv FILE.csv]] [--benchmark-file F.bm.json]\n"
+                 "                        [--load-state F.dat] [--save-state F.dat]\n"
                  "                        [--load-accum F.flxa] [--save-accum F.flxa]\n"
                  "                        [--out FILE.ppm|.pfm] [--save-scene FILE.flxs] scene...\n";
 }
 
-static bool endsWith(const std::string &s, const std::string &e) { return s.size() >= e.size() && s.compare(s.size() - e.size(), e.size(), e) == 0; }
+
+// --dump-settings: the settings in force as one JSON line (what the reference's Settings getters return after the import)
+static void dumpSettings(const flx::Settings &s, const std::string &scene, const std::string &output)
+{
+    const flx::Settings::Camera &c = s.camera; const flx::Settings::AreaLight &l = s.areaLight;
+    printf("{\"scene\": \"%s\", \"output\": \"%s\", \"envMap\": \"%s\", \"renderScale\": %g, \"windowWidth\": %d, \"windowHeight\": %d, \"wfBufferSize\": %u, "
+           "\"useWavefront\": %s, \"useRussianRoulette\": %s, \"useSeparateQueues\": %s, \"clUseBitstack\": %s, \"maxPathDepth\": %d, \"maxSpp\": %u, "
+           "\"maxRenderTime\": %u, \"sampleImplicit\": %s, \"sampleExplicit\": %s, \"useEnvMap\": %s, \"useAreaLight\": %s, \"tonemap\": %d, "
+           "\"camera\": {\"pos\": [%.9g, %.9g, %.9g], \"dir\": [%.9g, %.9g, %.9g], \"up\": [%.9g, %.9g, %.9g], \"right\": [%.9g, %.9g, %.9g], \"fov\": %.9g, "
+           "\"apertureSize\": %.9g, \"focalDist\": %.9g}, \"areaLight\": {\"pos\": [%.9g, %.9g, %.9g], \"N\": [%.9g, %.9g, %.9g], \"up\": [%.9g, %.9g, %.9g], "
+           "\"right\": [%.9g, %.9g, %.9g], \"E\": [%.9g, %.9g, %.9g], \"size\": [%.9g, %.9g]}, \"settings_by\": \"%s\"}\n",
+           scene.c_str(), output.c_str(), s.envMapName.c_str(), s.renderScale, s.windowWidth, s.windowHeight, s.wfBufferSize,
+           s.useWavefront ? "true" : "false", s.useRussianRoulette ? "true" : "false", s.useSeparateQueues ? "true" : "false", s.clUseBitstack ? "true" : "false",
+           s.maxPathDepth, s.maxSpp, s.maxRenderTime, s.sampleImplicit ? "true" : "false", s.sampleExplicit ? "true" : "false",
+           s.useEnvMap ? "true" : "false", s.useAreaLight ? "true" : "false", s.tonemap,
+           c.pos[0], c.pos[1], c.pos[2], c.dir[0], c.dir[1], c.dir[2], c.up[0], c.up[1], c.up[2], c.right[0], c.right[1], c.right[2], c.fov, c.apertureSize, c.focalDist,
+           l.pos[0], l.pos[1], l.pos[2], l.N[0], l.N[1], l.N[2], l.up[0], l.up[1], l.up[2], l.right[0], l.right[1], l.right[2], l.E[0], l.E[1], l.E[2], l.size[0], l.size[1],
+           s.parsedByReference ? "reference settings.cpp" : "scanner");
+}
+
+// Tracer::runBenchmarkFromFile (src/tracer.cpp:567-870) without the window
+static int runBenchmarkFile(const std::string &benchmarkFile, int device, uint32_t tasks, uint32_t lbvhLeaf, bool dumpOnly)
+{
+#ifndef FLX_WITH_REFERENCE_HOST
+    (void)device; (void)tasks; (void)lbvhLeaf; (void)dumpOnly;
+    std::cerr << "fluctus_headless: --benchmark-file needs the build with the reference tree (its Settings::import and scene loaders); got " << benchmarkFile << "\n";
+    return 2;
+#else
+    std::vector<flx::BenchmarkScene> jobs;
+    try { jobs = flx::loadBenchmarkFileWithReference(benchmarkFile); }
+    catch (const std::exception &e) { std::cerr << "fluctus_headless: " << e.what() << "\n"; return 2; }
+    int rc = 0;
+    for (size_t k = 0; k < jobs.size(); k++)
+    {
+        const flx::BenchmarkScene &job = jobs[k];
+        if (dumpOnly) { dumpSettings(job.settings, job.file, job.outputPrefix); continue; }
+        try
+        {
+            flx::Settings st = job.settings;
+            if (tasks) st.wfBufferSize = tasks;
+            const int width = st.windowWidth, height = st.windowHeight; // resetParams(settings.getWindowWidth(), ...) at renderScale 1
+            if (!st.useWavefront && (uint64_t)st.wfBufferSize < (uint64_t)width * height) st.wfBufferSize = (uint32_t)(width * height);
+            flx::HostScene scene = endsWith(job.file, ".flxs") ? flx::loadScene(job.file) : flx::loadSceneWithReference(job.file, st.envMapName);
+            if (lbvhLeaf) scene.nodes = flx::CudaContext::buildHierarchy(scene.tris.data(), scene.tris.size(), scene.indices, lbvhLeaf, device, nullptr);
+            flx::HeadlessTracer tracer(width, height, st, device);
+            tracer.init(scene);
+            if (!scene.hasEnvMap()) tracer.params.useEnvMap = 0;
+            std::ostringstream csv;
+            const std::string summary = tracer.runBenchmarkScene((double)st.maxRenderTime, st.useWavefront, csv);
+            std::cout << summary << std::endl;
+            tracer.saveImage(job.outputPrefix + ".ppm");
+            tracer.saveImage(job.outputPrefix + ".pfm");
+            { std::ofstream f(job.outputPrefix + ".csv"); f << csv.str(); if (!f) std::cout << "Failed to write CSV benchmark report!" << std::endl; }
+            { std::ofstream f(job.outputPrefix + ".txt"); f << summary << "\n"; if (!f) std::cout << "Failed to write TXT benchmark report!" << std::endl; }
+            const flx::CudaContext::Totals &t = tracer.lastTotals;
+            const double sec = tracer.lastSeconds;
+            printf("{\"scene\": \"%s\", \"output\": \"%s\", \"width\": %d, \"height\": %d, \"triangles\": %zu, \"renderer\": \"%s\", \"bounces\": %d, "
+                   "\"max_spp\": %u, \"max_render_time\": %u, \"primary\": %llu, \"extension\": %llu, \"shadow\": %llu, \"samples\": %llu, \"splatted\": %llu, "
+                   "\"seconds\": %.4f, \"msamples_per_s\": %.3f, \"mrays_per_s\": %.3f, \"settings_by\": \"%s\", \"kernel_launches\": %llu}\n",
+                   job.file.c_str(), job.outputPrefix.c_str(), width, height, scene.tris.size(), st.useWavefront ? "wavefront" : "mk", st.maxPathDepth,
+                   st.maxSpp, st.maxRenderTime, (unsigned long long)t.primary, (unsigned long long)t.extension, (unsigned long long)t.shadow,
+                   (unsigned long long)t.samples, (unsigned long long)t.splatted, sec, t.samples / std::max(sec, 1e-9) * 1e-6,
+                   (t.primary + t.extension + t.shadow) / std::max(sec, 1e-9) * 1e-6, st.parsedByReference ? "reference settings.cpp" : "scanner",
+                   (unsigned long long)tracer.getClContext().launchCount());
+        }
+        catch (const std::exception &e)
+        {
+            std::cerr << "fluctus_headless: " << job.file << ": " << e.what() << "\n";
+            rc = 1;
+        }
+    }
+    return rc;
+#endif
+}
 
 int main(int argc, char **argv)
 {
     flx::Settings settings;
     int width = -1, height = -1, spp = 32, device = -1, bounces = -1, gpus = 1, rank = 0, world = 1;
     uint32_t iterations = 0, tasks = 0, lbvhLeaf = 0;
-    bool useMK = false;
+    bool useMK = false, dumpOnly = false;
     double benchSeconds = 0.0;
-    std::string out = "output.ppm", saveScene, env, csvFile, loadState, saveState, loadAccum, saveAccum, commFile;
+    std::string out = "output.ppm", saveScene, env, csvFile, loadState, saveState, loadAccum, saveAccum, commFile, benchmarkFile;
     std::vector<std::string> scenes;
     try
     {
@@ -110,6 +195,8 @@ int main(int argc, char **argv)
             else if (a == "--comm-file") commFile = next();
             else if (a == "--benchmark") benchSeconds = std::stod(next());
             else if (a == "--csv") csvFile = next();
+            else if (a == "--benchmark-file") benchmarkFile = next();
+            else if (a == "--dump-settings") dumpOnly = true;
             else if (a == "--load-state") loadState = next();
             else if (a == "--save-state") saveState = next();
             else if (a == "--load-accum") loadAccum = next();
@@ -119,7 +206,12 @@ int main(int argc, char **argv)
             else if (!a.empty() && a[0] == '-') throw std::runtime_error("unknown option " + a);
             else scenes.push_back(a);
         }
-        if (scenes.empty()) throw std::runtime_error("no scene given");
+        if (!benchmarkFile.empty())
+        {
+            if (!scenes.empty() || gpus > 1 || world > 1 || benchSeconds > 0.0 || !loadAccum.empty())
+                throw std::runtime_error("--benchmark-file names its own scenes and runs on one GPU (no scene arguments, --gpus, --world, --benchmark, --load-accum)");
+        }
+        else if (scenes.empty() && !dumpOnly) throw std::runtime_error("no scene given");
         if (width < 0) width = settings.windowWidth;
         if (height < 0) height = settings.windowHeight;
         if (width <= 0 || height <= 0 || spp < 0) throw std::runtime_error("invalid width / height / samples");
@@ -140,6 +232,9 @@ int main(int argc, char **argv)
         usage();
         return 2;
     }
+
+    if (!benchmarkFile.empty()) return runBenchmarkFile(benchmarkFile, device, tasks, lbvhLeaf, dumpOnly);
+    if (dumpOnly) { dumpSettings(settings, scenes.empty() ? "" : scenes[0], out); return 0; }
 
     int rc = 0;
     for (size_t si = 0; si < scenes.size(); si++)

@@ -13,73 +13,13 @@
 #include <string>
 #include "cuda_context.hpp"
 #include "host_scene.hpp"
+#include "host_settings.hpp"
 
 namespace flx {
 
-// ---- Settings: the reference's settings.json surface -----------------------------------------------------
-struct Settings
-{
-    std::string envMapName;
-    float renderScale = 1.0f;
-    int windowWidth = 640, windowHeight = 480;
-    uint32_t wfBufferSize = 1u << 20;
-    bool useRussianRoulette = false, useSeparateQueues = false, clUseBitstack = false;
-    int maxPathDepth = 10;
-    uint32_t maxSpp = 0, maxRenderTime = 0;
-    bool sampleImplicit = true, sampleExplicit = true, useEnvMap = false, useAreaLight = true;
-    int tonemap = 2;
-
-    // Reads the "release" object of a settings.json (reference src/settings.cpp:61-87).  A deliberately small
-    // scanner: `"key": value` pairs with number / bool / string values, nested objects ignored.
-    void load(const std::string &path, const std::string &section = "release")
-    {
-        std::ifstream in(path);
-        if (!in) throw std::runtime_error("cannot open settings file " + path);
-        std::stringstream ss; ss << in.rdbuf();
-        const std::string all = ss.str();
-        size_t a = all.find("\"" + section + "\"");
-        if (a == std::string::npos) return;
-        a = all.find('{', a);
-        int depth = 0; size_t b = a;
-        for (; b < all.size(); b++) { if (all[b] == '{') depth++; else if (all[b] == '}' && --depth == 0) break; }
-        const std::string obj = all.substr(a, b - a);
-        std::string s;
-        if (find(obj, "envMap", s)) envMapName = s;
-        if (find(obj, "renderScale", s)) renderScale = std::stof(s);
-        if (find(obj, "windowWidth", s)) windowWidth = std::stoi(s);
-        if (find(obj, "windowHeight", s)) windowHeight = std::stoi(s);
-        if (find(obj, "wfBufferSize", s)) wfBufferSize = (uint32_t)std::stoul(s);
-        if (find(obj, "useRussianRoulette", s)) useRussianRoulette = s == "true";
-        if (find(obj, "useSeparateQueues", s)) useSeparateQueues = s == "true";
-        if (find(obj, "clUseBitstack", s)) clUseBitstack = s == "true";
-        if (find(obj, "maxPathDepth", s)) maxPathDepth = std::stoi(s);
-        if (find(obj, "maxSpp", s)) maxSpp = (uint32_t)std::stoul(s);
-        if (find(obj, "maxRenderTime", s)) maxRenderTime = (uint32_t)std::stoul(s);
-        if (find(obj, "sampleImplicit", s)) sampleImplicit = s == "true";
-        if (find(obj, "sampleExplicit", s)) sampleExplicit = s == "true";
-        if (find(obj, "useEnvMap", s)) useEnvMap = s == "true";
-        if (find(obj, "useAreaLight", s)) useAreaLight = s == "true";
-        if (find(obj, "tonemap", s)) tonemap = std::stoi(s);
-    }
-
-private:
-    static bool find(const std::string &obj, const std::string &key, std::string &out)
-    {
-        const size_t k = obj.find("\"" + key + "\"");
-        if (k == std::string::npos) return false;
-        size_t p = obj.find(':', k);
-        if (p == std::string::npos) return false;
-        p++;
-        while (p < obj.size() && isspace((unsigned char)obj[p])) p++;
-        if (p >= obj.size()) return false;
-        if (obj[p] == '"') { const size_t e = obj.find('"', p + 1); out = obj.substr(p + 1, e - p - 1); return true; }
-        size_t e = p;
-        while (e < obj.size() && obj[e] != ',' && obj[e] != '}' && !isspace((unsigned char)obj[e])) e++;
-        out = obj.substr(p, e - p);
-        return !out.empty();
-    }
-};
-
+// cam.fovSCALE = tan(toRad(0.5f * cam.fov)) (src/tracer.cpp:1137): the argument in float as there, the tangent in double
+// and rounded once — independent of which libm tanf a host has, and what the Python mirror computes (abi.py)
+inline float fovScale(float fov) { return (float)std::tan((double)(0.5f * fov * 0.01745329251994329576923690768489f)); }
 inline flx_float3 f3(float x, float y, float z, float w = 0.0f) { flx_float3 v = {x, y, z, w}; return v; }
 
 class HeadlessTracer
@@ -117,22 +57,26 @@ public:
     void initCamera()
     {
         flx_camera &c = params.camera;
-        c.pos = f3(0.0f, 1.0f, 3.5f); c.right = f3(1.0f, 0.0f, 0.0f); c.up = f3(0.0f, 1.0f, 0.0f); c.dir = f3(0.0f, 0.0f, -1.0f);
-        c.fov = 60.0f; c.fovSCALE = std::tan(0.5f * c.fov * 0.01745329251994329576923690768489f);
-        c.apertureSize = 0.0f; c.focalDist = 0.5f;
+        const Settings::Camera &s = settings.camera; // Settings::getCameraSettings()
+        c.pos = f3(s.pos[0], s.pos[1], s.pos[2]); c.right = f3(s.right[0], s.right[1], s.right[2]);
+        c.up = f3(s.up[0], s.up[1], s.up[2]); c.dir = f3(s.dir[0], s.dir[1], s.dir[2]);
+        c.fov = s.fov; c.fovSCALE = fovScale(c.fov);
+        c.apertureSize = s.apertureSize; c.focalDist = s.focalDist;
     }
     void setCamera(const float pos[3], const float dir[3], const float up[3], const float right[3], float fov)
     {
         flx_camera &c = params.camera;
         c.pos = f3(pos[0], pos[1], pos[2]); c.dir = f3(dir[0], dir[1], dir[2]); c.up = f3(up[0], up[1], up[2]); c.right = f3(right[0], right[1], right[2]);
-        c.fov = fov; c.fovSCALE = std::tan(0.5f * fov * 0.01745329251994329576923690768489f);
+        c.fov = fov; c.fovSCALE = fovScale(fov);
     }
     void initPostProcessing() { params.ppParams.exposure = 1.0f; params.ppParams.tmOperator = (uint32_t)settings.tonemap; }
     void initAreaLight()
     {
         flx_area_light &l = params.areaLight;
-        l.right = f3(0.0f, 0.0f, -1.0f); l.up = f3(0.0f, 1.0f, 0.0f); l.N = f3(-1.0f, 0.0f, 0.0f); l.pos = f3(1.0f, 1.0f, 0.0f, 1.0f);
-        l.E = f3(100.0f, 100.0f, 100.0f); l.size.x = 0.5f; l.size.y = 0.5f;
+        const Settings::AreaLight &s = settings.areaLight; // Settings::getAreaLightSettings()
+        l.right = f3(s.right[0], s.right[1], s.right[2]); l.up = f3(s.up[0], s.up[1], s.up[2]);
+        l.N = f3(s.N[0], s.N[1], s.N[2], s.N[3]); l.pos = f3(s.pos[0], s.pos[1], s.pos[2], s.pos[3]);
+        l.E = f3(s.E[0], s.E[1], s.E[2]); l.size.x = s.size[0]; l.size.y = s.size[1];
     }
 
     // Tracer::init (src/tracer.cpp:68-93): scene -> env map -> hierarchy -> worldRadius -> upload
@@ -293,6 +237,76 @@ public:
         return line;
     }
 
+    // One scene of Tracer::runBenchmarkFromFile (src/tracer.cpp:700-870): render until maxRenderTime seconds have passed
+    // or w*h*maxSpp samples are in the frame, whichever comes first (30 s when neither is set, :706-711), with the
+    // renderer the settings name (useWavefront; else the microkernel one, a whole sample per pixel per step), logging
+    // `time;primary;extension;shadow;total;samples` every half second (:683-697) and returning the summary line (:833).
+    // Post-processing runs once at the end (the reference's per-iteration tonemap exists for its window; skipPP is moot).
+    std::string runBenchmarkScene(double maxRenderTime, bool wavefront, std::ostream &csv, uint32_t batch = 8)
+    {
+        using clock = std::chrono::steady_clock;
+        auto now = [] { return std::chrono::duration<double>(clock::now().time_since_epoch()).count(); };
+        if (maxRenderTime == 0.0 && params.maxSpp == 0) maxRenderTime = 30.0;
+        const uint64_t maxSampleCount = (uint64_t)params.width * params.height * params.maxSpp;
+        if (!wavefront)
+        {
+            if ((uint64_t)clctx.getNumTasks() < (uint64_t)params.width * params.height)
+                throw std::runtime_error("microkernel renderer: wfBufferSize must be >= width * height");
+            params.useRoulette = 0; // the renderSingle graph has a fixed number of bounces (src/tracer.cpp:118-122)
+        }
+        clctx.updateParams(params);
+        struct Tot { uint64_t primary, extension, shadow, samples, counted; };
+        auto read = [&]() -> Tot
+        {
+            if (wavefront) { const CudaContext::Totals t = clctx.getRenderTotals(); return Tot{t.primary, t.extension, t.shadow, t.samples, t.splatted}; }
+            clctx.fetchStats();
+            const RenderStats &st = clctx.statsAsync;
+            return Tot{st.primaryRays, st.extensionRays, st.shadowRays, st.samples, st.samples};
+        };
+        if (wavefront)
+        {
+            clctx.setPixelIndex(0);
+            clctx.render(0, true);
+            clctx.setPixelIndex(cursorStart());
+        }
+        else clctx.renderSingle(0, true);
+        clctx.finishQueue();
+        Tot first = read(), prev = first, t = first;
+        csv << "time;primary;extension;shadow;total;samples\n";
+        const double startT = now();
+        double lastLogTime = startT, currT = startT;
+        auto logStats = [&](double elapsed, double deltaT)
+        {
+            const double s = 1e6 * deltaT;
+            const double pr = double(t.primary - prev.primary), ex = double(t.extension - prev.extension), sh = double(t.shadow - prev.shadow);
+            csv << elapsed << ";" << pr / s << ";" << ex / s << ";" << sh / s << ";" << (pr + ex + sh) / s << ";" << double(t.samples - prev.samples) / s << "\n";
+            prev = t; lastLogTime = currT;
+        };
+        uint64_t lastCounted = ~0ull;
+        while ((maxRenderTime == 0.0 || currT - startT < maxRenderTime) && (maxSampleCount == 0 || t.counted - first.counted < maxSampleCount))
+        {
+            if (wavefront) clctx.render(batch); else clctx.renderSingle(1, false);
+            t = read(); // synchronises
+            iteration += wavefront ? batch : 1;
+            currT = now();
+            if (currT - lastLogTime > 0.5) logStats(currT - startT, currT - lastLogTime);
+            if (wavefront && maxSampleCount && t.counted == lastCounted) break; // CHECK_SPP budget used up (quirk 13, see resume())
+            lastCounted = t.counted;
+        }
+        if (currT > lastLogTime) logStats(currT - startT, currT - lastLogTime);
+        clctx.enqueuePostprocessKernel(params);
+        clctx.finishQueue();
+        lastTotals = CudaContext::Totals{t.primary - first.primary, t.extension - first.extension, t.shadow - first.shadow, t.samples - first.samples,
+                                         t.counted - first.counted, iteration};
+        lastSeconds = currT - startT;
+        const double scale = 1e6 * std::max(currT - startT, 1e-9);
+        const double prim = lastTotals.primary / scale, ext = lastTotals.extension / scale, shdw = lastTotals.shadow / scale, samp = lastTotals.samples / scale;
+        char line[512];
+        snprintf(line, sizeof(line), "%.1fM primary, %.2fM extension, %.2fM shadow, %.2fM samples, total: %.2fM rays/s", prim, ext, shdw, samp, prim + ext + shdw);
+        return line;
+    }
+    CudaContext::Totals lastTotals{}; double lastSeconds = 0.0; // of the last runBenchmarkScene
+
     // Tracer::saveState / loadState (src/tracer.cpp:996-1054, keys F2/F3): camera, lights, sampling switches and
     // post-processing as one flat little-endian record, field order as in iterateStateItems, so a
     // data/states/state_<hash>.dat written by the reference's viewer positions this renderer's camera and vice versa.
@@ -383,7 +397,7 @@ private:
         auto vec = [&](flx_float3 &v) { rw(&v.x, 4); rw(&v.y, 4); rw(&v.z, 4); };
         flx_camera &c = params.camera; flx_area_light &l = params.areaLight;
         f(cameraRotationX); f(cameraRotationY); f(cameraSpeed); f(c.fov);
-        if (!write) c.fovSCALE = std::tan(0.5f * c.fov * 0.01745329251994329576923690768489f);
+        if (!write) c.fovSCALE = fovScale(c.fov);
         f(c.focalDist); f(c.apertureSize); vec(c.dir); vec(c.pos); vec(c.right); vec(c.up);
         vec(l.N); vec(l.pos); vec(l.right); vec(l.up); vec(l.E); f(l.size.x); f(l.size.y); f(params.envMapStrength);
         u(params.maxBounces); u(params.useAreaLight); u(params.useEnvMap); u(params.sampleExpl); u(params.sampleImpl); u(params.useRoulette);

@@ -43,6 +43,46 @@ def test_headless_one_process_per_gpu_flags():
     assert "nccl" not in subprocess.check_output(["ldd", BIN], text=True) + subprocess.check_output(["ldd", lib], text=True)
 
 
+def test_settings_and_benchmark_file_are_parsed_by_the_reference_settings_class(tmp_path):
+    """settings.json / .bm.json go through the reference's own Settings::import (src/settings.cpp compiled in place):
+    nested camera / areaLight objects, lookAt -> dir / up / right, scalar E, per-scene overrides on top of the file's
+    base settings, envMap and outputFolder relative to the benchmark file (Tracer::runBenchmarkFromFile, tracer.cpp:567-630)."""
+    import json
+    _need_bin()
+    cfg = tmp_path / "s.json"
+    cfg.write_text(json.dumps({"release": {"maxPathDepth": 7, "wfBufferSize": 4096, "camera": {"pos": [1, 2, 3], "lookAt": [0, 0, 0], "fov": 40}}}))
+    r = subprocess.run([BIN, "--settings", str(cfg), "--dump-settings"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["maxPathDepth"] == 7 and d["wfBufferSize"] == 4096 and d["tonemap"] == 2 and d["useAreaLight"] is True   # rest: Settings::init defaults
+    if d["settings_by"] != "reference settings.cpp":
+        pytest.skip("binary built without the reference tree: scalar keys only")
+    want = -np.array([1, 2, 3.0]) / np.linalg.norm([1, 2, 3.0])
+    assert np.allclose(d["camera"]["dir"], want, atol=1e-6) and d["camera"]["fov"] == 40 and d["camera"]["pos"] == [1, 2, 3]
+    assert abs(np.dot(d["camera"]["dir"], d["camera"]["up"])) < 1e-6 and abs(np.dot(d["camera"]["dir"], d["camera"]["right"])) < 1e-6
+    bm = tmp_path / "job.bm.json"
+    bm.write_text(json.dumps({
+        "settings": {"windowWidth": 320, "windowHeight": 200, "useWavefront": True, "maxSpp": 4, "maxPathDepth": 5, "envMap": "env/night.hdr",
+                     "areaLight": {"pos": [0, 3, 0], "N": [0, -1, 0], "E": [50], "size": [1, 2]}},
+        "outputFolder": "out",
+        "scenes": [{"file": "a.ply", "outputFile": "first"},
+                   {"file": "sub/b.obj", "outputFile": "second", "settings": {"useWavefront": False, "maxPathDepth": 3, "tonemap": 1}},
+                   {"file": "c.ply", "outputFile": "third"}]}))
+    r = subprocess.run([BIN, "--benchmark-file", str(bm), "--dump-settings"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    a, b, c = (json.loads(l) for l in r.stdout.strip().splitlines()[-3:])
+    base = str(tmp_path) + "/"
+    assert (a["scene"], b["scene"], c["scene"]) == (base + "a.ply", base + "sub/b.obj", base + "c.ply")
+    assert a["output"] == base + "out/first" and (tmp_path / "out").is_dir() and a["envMap"] == base + "env/night.hdr"
+    assert (a["windowWidth"], a["windowHeight"], a["maxSpp"], a["maxPathDepth"], a["useWavefront"]) == (320, 200, 4, 5, True)
+    assert a["areaLight"]["E"] == [50, 50, 50] and a["areaLight"]["size"] == [1, 2] and a["areaLight"]["N"] == [0, -1, 0]
+    assert (b["useWavefront"], b["maxPathDepth"], b["tonemap"]) == (False, 3, 1)
+    # the base settings are imported again before every scene; a key only a scene set stays (one singleton, as in the reference)
+    assert (c["useWavefront"], c["maxPathDepth"], c["tonemap"]) == (True, 5, 1)
+    r = subprocess.run([BIN, "--benchmark-file", str(bm), "scene.flxs"], capture_output=True, text=True)
+    assert r.returncode == 2 and "names its own scenes" in r.stderr
+
+
 def test_flxs_roundtrip_python(tmp_path, teapot, night_env):
     from fluctus_b200 import scene as fs
     p = str(tmp_path / "t.flxs")

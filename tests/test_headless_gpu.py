@@ -203,6 +203,45 @@ def test_headless_accumulation_checkpoint_resumes(tmp_path, teapot, night_env):
     assert r.returncode != 0 and "resolution" in r.stderr
 
 
+def test_headless_benchmark_file(tmp_path, teapot, night_env):
+    """fluctus_headless --benchmark-file: Tracer::runBenchmarkFromFile (src/tracer.cpp:567-870) — per scene the settings in
+    force, the renderer they name, the maxSpp / maxRenderTime stop rule, and the reference's output files."""
+    from fluctus_b200 import scene as fs
+    fs.save_flxs(str(tmp_path / "teapot.flxs"), teapot, night_env)
+    bm = tmp_path / "job.bm.json"
+    bm.write_text(json.dumps({
+        "settings": {"windowWidth": 96, "windowHeight": 64, "wfBufferSize": 8192, "useWavefront": True, "maxSpp": 6, "maxPathDepth": 4,
+                     "useAreaLight": False, "useEnvMap": True},
+        "outputFolder": "results",
+        "scenes": [{"file": "teapot.flxs", "outputFile": "wf"},
+                   {"file": "teapot.flxs", "outputFile": "mk", "settings": {"useWavefront": False, "maxSpp": 3}},
+                   {"file": "teapot.flxs", "outputFile": "timed", "settings": {"maxSpp": 0, "maxRenderTime": 1}}]}))
+    r = _run(["--benchmark-file", bm])
+    lines = r.stdout.strip().splitlines()
+    stats = [json.loads(l) for l in lines if l.startswith("{")]
+    summaries = [l for l in lines if "M primary" in l]
+    if stats[0]["settings_by"] != "reference settings.cpp":
+        pytest.skip("binary built without the reference tree")
+    assert len(stats) == 3 and len(summaries) == 3
+    wf, mk, timed = stats
+    assert (wf["renderer"], wf["width"], wf["height"], wf["bounces"], wf["max_spp"]) == ("wavefront", 96, 64, 4, 6)
+    assert 6 * 96 * 64 - 6 - 64 <= wf["splatted"] <= 8 * 96 * 64          # CHECK_SPP budget (pixel 0 starves, quirk 13; <= admits maxSpp + 1)
+    assert mk["renderer"] == "mk" and mk["samples"] == 3 * 96 * 64           # exactly maxSpp samples in every pixel
+    assert timed["max_render_time"] == 1 and 1.0 <= timed["seconds"] < 2.0 and timed["samples"] > 100 * 96 * 64
+    for name in ("wf", "mk", "timed"):
+        base = tmp_path / "results" / name
+        img = _read_pfm(str(base) + ".pfm")
+        assert img.shape == (64, 96, 3) and np.isfinite(img).all() and img.mean() > 0.01
+        assert (tmp_path / "results" / (name + ".ppm")).stat().st_size > 96 * 64 * 3
+        rows = open(str(base) + ".csv").read().strip().splitlines()
+        assert rows[0] == "time;primary;extension;shadow;total;samples" and len(rows) >= 2
+        t, prim, ext, shw, tot, smp = (float(x) for x in rows[-1].split(";"))
+        assert abs(tot - (prim + ext + shw)) <= 1e-3 * tot + 1e-9
+        assert open(str(base) + ".txt").read().strip() in summaries
+    a, b = _binned(_read_pfm(str(tmp_path / "results" / "wf.pfm"))), _binned(_read_pfm(str(tmp_path / "results" / "timed.pfm")))
+    assert float((((a - b) ** 2) / (b ** 2 + 1e-3)).mean()) < 0.08            # 6 spp vs a second of rendering: same picture
+
+
 def _gpu_count():
     import torch
     return torch.cuda.device_count()
