@@ -280,11 +280,11 @@ int main(int argc, char **argv)
                 for (auto &tr : tracers) ctxs.push_back(&tr->getClContext());
                 flx::CudaContext::reduceFrames(ctxs);
             }
-            if (world > 1) // join the communicator; one combine of the still empty frames warms NCCL's channels up and lines the ranks up
+            if (world > 1) // join the communicator; one combine of the still empty frames sets NCCL's connections up and lines the ranks up
             {
                 flx::CudaContext &c = tracer.getClContext();
                 c.commInit(rank, world, exchangeCommId(commFile + (scenes.size() > 1 ? "." + std::to_string(si) : ""), rank));
-                c.allreducePixels();
+                c.reducePixels(0); // the collective used below: NCCL sets its connections up per algorithm at the first call (1.2 s at 8 ranks)
                 c.finishQueue();
             }
             const auto t0 = std::chrono::steady_clock::now();
