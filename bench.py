@@ -702,6 +702,27 @@ def run_ours(args):
     tr.clctx.setTraversal(BITSTACK)
     c = tr.clctx
     pix = pixels_tensor(c, dev)
+    # The frame combine is the library's own collective (flx_comm_init / flx_reduce_pixels: ncclReduce from the C-ABI on
+    # the context's stream); torch.distributed carries the communicator id and the timing scalars.  If the library cannot
+    # set its communicator up the torch collective over the zero-copy view takes over, and the line says so.
+    collective = "none (1 GPU)"
+    if world > 1:
+        try:
+            uid = torch.zeros(128, dtype=torch.uint8, device=dev)
+            if rank == 0:
+                uid.copy_(torch.frombuffer(bytearray(fx.CudaContext.commUniqueId()), dtype=torch.uint8))
+            dist.broadcast(uid, src=0)
+            c.commInit(rank, world, bytes(uid.cpu().numpy().tobytes()))
+            collective = "flx_reduce_pixels (ncclReduce from the C-ABI, NCCL %d)" % c.commInfo()["nccl_version"]
+        except Exception as e:  # noqa: BLE001
+            collective = "torch.distributed.reduce (flx_comm_init failed: %s)" % str(e)[:120]
+    own_comm = collective.startswith("flx_")
+
+    def combine():
+        if own_comm:
+            c.reducePixels(0)
+        else:
+            reduce_pixels(pix, dst=0)
     cursor0 = tr._cursor_start()
     n_px = WIDTH * HEIGHT
     h_frame = torch.empty((n_px, 4), dtype=torch.float32).pin_memory()
@@ -717,7 +738,7 @@ def run_ours(args):
         tot = None
         if world > 1:
             tot = c.getRenderTotals()              # this rank's totals (synchronises; the reduce below moves pixels only)
-            reduce_pixels(pix, dst=0)              # ONE NCCL reduce of the accumulation buffer per frame, into the root
+            combine()                              # ONE NCCL reduce of the accumulation buffer per frame, into the root
         if rank == 0:                              # the frame exists on the root only: it alone tonemaps and reads back,
             c.enqueuePostprocessKernel()           # the other ranks go straight on to the next frame's reset
             if host_io:
@@ -770,7 +791,7 @@ def run_ours(args):
         e0.record(stream)
         tot = tr.render(spp=share, batch=8) if share > 0 else c.getRenderTotals()
         if world > 1:
-            reduce_pixels(pix, dst=0)
+            combine()
         if rank == 0:
             c.enqueuePostprocessKernel()
         e1.record(stream)
@@ -872,7 +893,7 @@ def run_ours(args):
             "metric": METRIC, "value": v["samples"] / (v["ms"] * 1e-3) / 1e6, "unit": "Msamples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": v["ms"] / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(world, scene, "ours"),
+            "config": dict(config_dict(world, scene, "ours"), collective=collective),
             "mrays_per_s": {"extension": v["ext"] / (v["ms"] * 1e-3) / 1e6, "shadow": v["shadow"] / (v["ms"] * 1e-3) / 1e6,
                             "total": (v["ext"] + v["shadow"]) / (v["ms"] * 1e-3) / 1e6},
             "e2e": {"value": h["samples"] / (h["ms"] * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": h["ms"] / args.steps,
