@@ -51,6 +51,9 @@ FLX_DEV void stageTopNodes(const DevBVH &bvh, float4 *top)
 // One 256-bit load (sm_100: LDG.E.256) = half an inner node.  Rays of a warp sit in different nodes, so every lane of
 // a load instruction costs the L1 its own tag look-up whatever the access width: fetching the 64-byte node with two
 // 32-byte loads instead of four 16-byte ones halves the L1 wavefronts of a node visit.
+#ifndef FLX_SLOT_LD_EARLY
+#define FLX_SLOT_LD_EARLY 1
+#endif
 #ifndef FLX_NODE_LD256
 #define FLX_NODE_LD256 0
 #endif
@@ -78,11 +81,12 @@ FLX_DEV bool slabTest(float bx0, float by0, float bz0, float bx1, float by1, flo
 // src/intersect.cl:63-93 (Moeller-Trumbore, EPSILON 1e-12f) with the two edge vectors s1 = v1 - v0 and
 // s2 = v2 - v0 supplied by the caller: the leaf slots store them precomputed (one IEEE subtraction per
 // component, done once at upload instead of once per test — same operands, same rounding, same bits).
-FLX_DEV bool triTestEdges(f3 o, f3 d, f3 p0, f3 s1, f3 s2, float &t, float &u, float &v)
+// `never` is a condition the caller knows to be false; see the leaf body of traceLoop for what it is good for.
+FLX_DEV bool triTestEdges(f3 o, f3 d, f3 p0, f3 s1, f3 s2, float &t, float &u, float &v, bool never = false)
 {
     const f3 pvec = cross(d, s2);
     const float det = dot(s1, pvec);
-    if (fabsf(det) < 1e-12f) return false;
+    if (fabsf(det) < 1e-12f || never) return false;
     const float iDet = recip(det);
     const f3 tvec = o - p0;
     u = dot(tvec, pvec) * iDet;
@@ -315,9 +319,15 @@ FLX_DEV void traceLoop(const DevBVH &bvh, const float4 *__restrict__ top, Job &j
                     if (COUNT) cnt.tri++;
                     const float4 *q = bvh.slots + 3 * (size_t)slot;
                     const float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2);
+                    // v0 is not needed before the determinant test, and ptxas sinks its load below that branch: a second,
+                    // dependent trip to L1 per triangle.  Making the branch look at the loaded word (a triangle index is
+                    // never 0xffffffff) keeps the three loads together; the result of the test is unchanged.
+                    // Pays where the traversal waits for memory (ray batches against a tree far larger than the caches: cfg5
+                    // +2.6 %), costs where it is bound by issue slots and L1 (the kitchen render: -0.6 %) — batch jobs only.
+                    const bool never = BATCH && FLX_SLOT_LD_EARLY && __float_as_uint(q0.w) == 0xffffffffu;
                     float t, u, v;
                     bool found = false;
-                    if (triTestEdges(o, d, mk3(q0), mk3(q1), mk3(q2), t, u, v) && t > 0.0f && t < best.t)
+                    if (triTestEdges(o, d, mk3(q0), mk3(q1), mk3(q2), t, u, v, never) && t > 0.0f && t < best.t)
                     {
                         best.t = t; best.u = u; best.v = v; best.slot = slot;
                         found = true;
