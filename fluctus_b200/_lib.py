@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfluctus_cuda.so")
+# FLX_LIB_VARIANT=exactlibm selects the TEST-ONLY build with double-precision transcendental functions (csrc/flx_libm.cuh)
+LIB_PATH = os.path.join(_HERE, "libfluctus_cuda_%s.so" % os.environ["FLX_LIB_VARIANT"] if os.environ.get("FLX_LIB_VARIANT") else "libfluctus_cuda.so")
 _lib = None
 
 V, U32, U64, I32, SZ, F32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_size_t, C.c_float

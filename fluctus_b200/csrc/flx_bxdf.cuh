@@ -49,11 +49,11 @@ FLX_DEV f3 ggxSampleLobe(float alpha, f3 N, uint32_t &seed) // :20-37
     f3 X, Y;
     makeOrthoBasis(N, X, Y);
     const float rx = rnd(seed), ry = rnd(seed);
-    const float theta = atan2f(alpha * sqrtf(rx), sqrtf(1.0f - rx));
+    const float theta = flx_atan2f(alpha * sqrtf(rx), sqrtf(1.0f - rx));
     const float phi = FLX_2PI * ry;
     float sinTheta, cosTheta, sinPhi, cosPhi;
-    sincosf(theta, &sinTheta, &cosTheta);
-    sincosf(phi, &sinPhi, &cosPhi);
+    flx_sincosf(theta, &sinTheta, &cosTheta);
+    flx_sincosf(phi, &sinPhi, &cosPhi);
     return (X * sinTheta * cosPhi + Y * sinTheta * sinPhi + N * cosTheta);
 }
 FLX_DEV float ggxG1(float alpha, f3 v, f3 n, f3 m) // :41-54

@@ -2,6 +2,7 @@
 // dispatch, read-back.  Replaces the reference's CLContext (src/clcontext.cpp); there is no CPU
 // or library fallback — without an sm_100 device flx_create fails.
 #include "flx_internal.h"
+#include "flx_libm.cuh"
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -143,12 +144,12 @@ void flx_destroy(flx_ctx *ctx)
 __global__ void k_prepare_materials(flx_material *materials, int nMaterials, float *gammaLut)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < 256) gammaLut[i] = powf((float)i * FLX_ONE_255, 2.2f);
+    if (i < 256) gammaLut[i] = flx_powf((float)i * FLX_ONE_255, 2.2f);
     if (i < nMaterials)
     {
         const flx_float3 kd = materials[i].Kd;
         flx_float3 g = kd;
-        g.x = powf(kd.x, 2.2f); g.y = powf(kd.y, 2.2f); g.z = powf(kd.z, 2.2f);
+        g.x = flx_powf(kd.x, 2.2f); g.y = flx_powf(kd.y, 2.2f); g.z = flx_powf(kd.z, 2.2f);
         materials[i].Kt = g;
     }
 }

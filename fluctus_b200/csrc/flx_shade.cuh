@@ -4,6 +4,7 @@
 // 1e-5 relative (the only differences are libm ulps in sinf/cosf/atan2f/acosf/powf).
 #pragma once
 #include "flx_internal.h"
+#include "flx_libm.cuh"
 
 // ---- src/random.cl:7-22 (Wang hash chain) ------------------------------------------------------
 FLX_DEV uint32_t wangHash(uint32_t s)
@@ -45,7 +46,7 @@ FLX_DEV void uniformSampleDisk(uint32_t &seed, float &dx, float &dy)
     const float sqrt_r = sqrtf(rnd(seed));
     const float th = FLX_2PI * rnd(seed);
     float s, c;
-    sincosf(th, &s, &c);
+    flx_sincosf(th, &s, &c);
     dx = sqrt_r * c; dy = sqrt_r * s;
 }
 
@@ -58,7 +59,7 @@ FLX_DEV f3 cosSampleHemisphere(f3 n, uint32_t &seed, float &pdf)
     f3 w = n, u, v;
     makeOrthoBasis(w, u, v);
     float sinR1, cosR1;
-    sincosf(r1, &sinR1, &cosR1);
+    flx_sincosf(r1, &sinR1, &cosR1);
     u *= (cosR1 * r2s);
     v *= (sinR1 * r2s);
     w *= sqrtf(1.0f - r2);
@@ -100,7 +101,7 @@ FLX_DEV f3 matGetFloat3(f3 fallback, float uvx, float uvy, int idx, const Materi
 FLX_DEV f3 matGetAlbedo(f3 fallbackGamma, float uvx, float uvy, int idx, const MaterialsDev &m)
 {
 #ifdef FLX_GAMMA_PER_PATH
-    return pow3(matGetFloat3(fallbackGamma, uvx, uvy, idx, m), 2.2f); // fallbackGamma = raw Kd in this build (loadMat)
+    return pow3x(matGetFloat3(fallbackGamma, uvx, uvy, idx, m), 2.2f); // fallbackGamma = raw Kd in this build (loadMat)
 #else
     if (idx == -1) return fallbackGamma;
     const uchar4 p = readTexel(uvx, uvy, m.textures[idx], m.texels);
@@ -122,14 +123,14 @@ FLX_DEV void sampleAreaLight(const flx_area_light &light, float &pdf, f3 &p, uin
 // ---- src/env_map.cl -----------------------------------------------------------------------------
 FLX_DEV void directionToUV(f3 dir, float &u, float &v) // :14-17, atan2pi/acospi as atan2f/acosf * (1/pi)
 {
-    u = (atan2f(dir.x, -dir.z) * FLX_INV_PI) * 0.5f + 0.5f;
-    v = acosf(dir.y) * FLX_INV_PI;
+    u = (flx_atan2f(dir.x, -dir.z) * FLX_INV_PI) * 0.5f + 0.5f;
+    v = flx_acosf(dir.y) * FLX_INV_PI;
 }
 FLX_DEV f3 uvToDirection(float u, float v, float &sinPhi) // :21-33
 {
     float cosPhi, sinTh, cosTh;
-    sincosf(v * FLX_PI, &sinPhi, &cosPhi);
-    sincosf(u * FLX_2PI - FLX_PI, &sinTh, &cosTh);
+    flx_sincosf(v * FLX_PI, &sinPhi, &cosPhi);
+    flx_sincosf(u * FLX_2PI - FLX_PI, &sinTh, &cosTh);
     return mk3(sinPhi * sinTh, cosPhi, -sinPhi * cosTh);
 }
 // read_imagef(normalised coords, clamp-to-edge, linear) in full fp32: the texture unit's 8-bit

@@ -87,7 +87,7 @@ k_postprocess(FrameBuffers fb, float exposure, uint32_t tmOperator, int denoiser
         col *= exposure;
         if (tmOperator == 1u) col = col / (mk3(1.0f) + col);
         if (tmOperator == 2u) col = uc2Func(2.0f * col) / uc2Func(mk3(11.2f));
-        if (tmOperator != 3u) col = pow3(col, FLX_ONE_2_2);
+        if (tmOperator != 3u) col = pow3x(col, FLX_ONE_2_2);
         fb.preview[gid] = mk4(col, c.w);
         if (denoiserAOV) // mk_postprocess.cl:49-55: normalised copies for an external denoiser
         {

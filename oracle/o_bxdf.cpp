@@ -35,10 +35,10 @@ static f3 ggxSampleLobe(float alpha, f3 N, uint32_t *seed) // :20-37
     f3 X, Y; const f3 Z = N;
     makeOrthoBasis(Z, &X, &Y);
     const float rx = rnd(seed), ry = rnd(seed);
-    const float theta = atan2f(alpha * sqrtf(rx), sqrtf(1 - rx));
+    const float theta = o_atan2f(alpha * sqrtf(rx), sqrtf(1 - rx));
     const float phi = k2PI * ry;
-    const float sinTheta = sinf(theta), cosTheta = cosf(theta);
-    const float sinPhi = sinf(phi), cosPhi = cosf(phi);
+    const float sinTheta = o_sinf(theta), cosTheta = o_cosf(theta);
+    const float sinPhi = o_sinf(phi), cosPhi = o_cosf(phi);
     return (X * sinTheta * cosPhi + Y * sinTheta * sinPhi + Z * cosTheta);
 }
 static float ggxG1(float alpha, f3 v, f3 n, f3 m) // :41-54

@@ -45,7 +45,21 @@ static inline f3 fmin3(f3 a, f3 b) { return mk3(fminf(a.x, b.x), fminf(a.y, b.y)
 static inline f3 fmax3(f3 a, f3 b) { return mk3(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z)); }
 static inline float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
 static inline bool isZero(f3 v) { return v.x == 0.0f && v.y == 0.0f && v.z == 0.0f; }
-static inline f3 pow3(f3 v, float e) { return mk3(powf(v.x, e), powf(v.y, e), powf(v.z, e)); }
+// transcendental functions: see fluctus_b200/csrc/flx_math.cuh (FLX_EXACT_LIBM) — the same switch on this side
+#ifdef ORC_EXACT_LIBM
+static inline float o_atan2f(float y, float x) { return (float)atan2((double)y, (double)x); }
+static inline float o_acosf(float x) { return (float)acos((double)x); }
+static inline float o_powf(float x, float y) { return (float)pow((double)x, (double)y); }
+static inline float o_sinf(float x) { return (float)sin((double)x); }
+static inline float o_cosf(float x) { return (float)cos((double)x); }
+#else
+static inline float o_atan2f(float y, float x) { return atan2f(y, x); }
+static inline float o_acosf(float x) { return acosf(x); }
+static inline float o_powf(float x, float y) { return powf(x, y); }
+static inline float o_sinf(float x) { return sinf(x); }
+static inline float o_cosf(float x) { return cosf(x); }
+#endif
+static inline f3 pow3(f3 v, float e) { return mk3(o_powf(v.x, e), o_powf(v.y, e), o_powf(v.z, e)); }
 
 // constants of reference src/geom.h:11-35
 static const float kPI = 3.14159265358979323846f;

@@ -20,7 +20,7 @@ f2 uniformSampleDisk(uint32_t *seed)
 {
     const float sqrt_r = sqrtf(rnd(seed));
     const float th = k2PI * rnd(seed);
-    f2 r; r.x = sqrt_r * cosf(th); r.y = sqrt_r * sinf(th);
+    f2 r; r.x = sqrt_r * o_cosf(th); r.y = sqrt_r * o_sinf(th);
     return r;
 }
 
@@ -32,7 +32,7 @@ f3 cosSampleHemisphere(f3 n, uint32_t *seed, float *p)
     const float r2s = sqrtf(r2);
     f3 w = n, u, v;
     makeOrthoBasis(w, &u, &v);
-    const float cosR1 = cosf(r1), sinR1 = sinf(r1);
+    const float cosR1 = o_cosf(r1), sinR1 = o_sinf(r1);
     u *= (cosR1 * r2s);
     v *= (sinR1 * r2s);
     w *= sqrtf(1 - r2);
@@ -110,8 +110,8 @@ void sampleAreaLight(const flx_area_light &light, float *pdf, f3 *p, uint32_t *s
 f2 directionToUV(f3 dir)
 {
     f2 uv;
-    uv.x = (atan2f(dir.x, -dir.z) * kInvPI) * 0.5f + 0.5f;
-    uv.y = acosf(dir.y) * kInvPI;
+    uv.x = (o_atan2f(dir.x, -dir.z) * kInvPI) * 0.5f + 0.5f;
+    uv.y = o_acosf(dir.y) * kInvPI;
     return uv;
 }
 
@@ -119,10 +119,10 @@ f2 directionToUV(f3 dir)
 f3 uvToDirection(float u, float v, float *sinPhi)
 {
     const float phi = v * kPI;
-    *sinPhi = sinf(phi);
-    const float cosPhi = cosf(phi);
+    *sinPhi = o_sinf(phi);
+    const float cosPhi = o_cosf(phi);
     const float th = u * k2PI - kPI;
-    const float sinTh = sinf(th), cosTh = cosf(th);
+    const float sinTh = o_sinf(th), cosTh = o_cosf(th);
     return mk3(*sinPhi * sinTh, cosPhi, -*sinPhi * cosTh);
 }
 

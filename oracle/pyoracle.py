@@ -41,10 +41,12 @@ def lib():
     """Load (building if needed and possible) oracle/liboracle.so."""
     global _LIB
     if _LIB is None:
-        path = os.path.join(_HERE, "liboracle.so")
+        # FLX_ORACLE_VARIANT=exactlibm: the build with double-precision transcendental functions (o_math.h, test_exact_libm_gpu.py)
+        name = "liboracle_%s.so" % os.environ["FLX_ORACLE_VARIANT"] if os.environ.get("FLX_ORACLE_VARIANT") else "liboracle.so"
+        path = os.path.join(_HERE, name)
         if not os.path.exists(path):
             import subprocess
-            subprocess.check_call(["make", "-s", "-C", _HERE, "liboracle.so"])
+            subprocess.check_call(["make", "-s", "-C", _HERE, name])
         L = C.CDLL(path)
         L.orc_wf_create.restype = V
         for name in ("orc_wf_state", "orc_wf_queue", "orc_wf_counters", "orc_wf_pixels", "orc_wf_spp",
