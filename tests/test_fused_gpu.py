@@ -166,17 +166,27 @@ def test_update_loop_matches_oracle_update(oracle, teapot, night_env, N):
         g = np.array([int(cg[q]) for q in ("raygenQueue", "extensionQueue", "shadowQueue")])
         o = np.array([int(co[q]) for q in ("raygenQueue", "extensionQueue", "shadowQueue")])
         if k == 0:
-            # the priming passes start from identical state: the preview's queue lengths are exact up to flipped branches
-            assert np.abs(g - o).max() <= max(4, 0.005 * N), (g, o)
+            # the three priming passes start from identical state, but the paths restarted in passes 1 and 2 get their
+            # pixels in the order of the GPU's atomics: from then on the two sides trace different (equally distributed)
+            # paths, and the lengths of the raygen / shadow queues of the last pass are two draws of the same binomial —
+            # 6 sigma of their difference.  The extension queue holds every live path: exact.
+            assert g[1] == o[1], (g, o)
+            assert np.all(np.abs(g - o) <= 6.0 * np.sqrt(2.0 * np.maximum(o, 1)) + 4), (g, o)
         tot_g += g; tot_o += o
-    assert np.all(np.abs(tot_g - tot_o) <= 0.01 * tot_o + 64), (tot_g, tot_o)
+    # two independent Monte-Carlo runs (the GPU's path <-> pixel assignment comes from atomics): the totals are sums of
+    # ~Poisson counts, so their difference has a standard deviation of about sqrt(2 * total) — 6 sigma + 1 %
+    assert np.all(np.abs(tot_g - tot_o) <= 6.0 * np.sqrt(2.0 * tot_o) + 0.01 * tot_o + 64), (tot_g, tot_o)
     assert tr.iteration == st["iteration"] == calls
     img, ref = tr.pixels(), wf.pixels().reshape(H, W, 4)
-    assert abs(float(img[..., 3].sum()) - float(ref[..., 3].sum())) <= 0.01 * float(ref[..., 3].sum()) + 64
+    ws = float(ref[..., 3].sum())
+    assert abs(float(img[..., 3].sum()) - ws) <= 6.0 * np.sqrt(2.0 * ws) + 0.01 * ws + 64
     a = (img[..., :3] / np.maximum(img[..., 3:], 1)).reshape(H // 8, 8, W // 8, 8, 3).mean((1, 3))
     b = (ref[..., :3] / np.maximum(ref[..., 3:], 1)).reshape(H // 8, 8, W // 8, 8, 3).mean((1, 3))
     relmse = float((((a - b) ** 2) / (b ** 2 + 1e-3)).mean())
-    assert relmse < 0.03, relmse
+    # 8 x 8 blocks hold ~64 * calls * min(N, w*h) * P(terminate) / (w*h) samples each (a few hundred at N = 2048): the
+    # difference of two independent block means is noise of that size, observed 0.005 - 0.02 with a tail — a wrong update
+    # sequence (no priming, no bounce cap, wrong first-iteration limit) shows up as > 0.3
+    assert relmse < 0.1, relmse
     # preview restart: a parameter edit sets iteration back to 0 and the next update() clears the frame
     tr.setParams(exposure=1.5)
     assert tr.iteration == 0
