@@ -5,7 +5,7 @@ The CUDA kernels and the CPU oracle perform the same IEEE binary32 operations in
 transcendental functions (sincos, atan2, acos, pow: CUDA's libdevice vs the host's libm).  Both libraries have a TEST-ONLY
 build that evaluates exactly those functions in double precision and rounds once (fluctus_b200/csrc/flx_libm.cuh:
 FLX_EXACT_LIBM, oracle/o_math.h: ORC_EXACT_LIBM).  With the two variants the stage-by-stage lock-step comparison of
-tests/test_stages_gpu.py — every field of every path after every stage — has to come out BIT-EXACT; with the shipped
+tests/test_stages_gpu.py — every field of every path after every stage, and after whole iterations of the fused kernels the benchmark runs — has to come out BIT-EXACT; with the shipped
 builds the same comparison shows paths that differ in the last place (and the few that a bilinear lookup or a
 `rand() < F` branch amplifies).  So every out-of-tolerance path of the GPU suite is a libm rounding and nothing else.
 
@@ -43,6 +43,10 @@ def _probe():
         scene, view = kitchen_standin(teapot, grid=(3, 2, 2))
         runs["kitchen stand-in (all BxDF classes, textured floor), 8 bounces"] = lambda: ts._run_lockstep(
             pyoracle, scene, env, 8192, 96, 54, 8, max_bounces=8, use_env_map=True, use_area_light=True, separate_queues=True, **view)
+        # the kernels the benchmark runs (flx_render's iteration: logic + in-place restart, materials, ext + shadow rays)
+        import test_fused_gpu as tf
+        runs["fused benchmark iteration (flx_render(1)), kitchen stand-in"] = lambda: tf._fused_lockstep(
+            pyoracle, scene, env, 16384, 96, 54, 6, warm=5, max_bounces=8, use_env_map=True, use_area_light=True, separate_queues=True, **view)
     except Exception as e:  # noqa: BLE001
         out["kitchen"] = "skipped: %s" % e
     for name, fn in runs.items():
